@@ -1,0 +1,142 @@
+/*
+ * zerotig.h - C ABI of libzerotig.so, the B200 (sm_100a) kernels behind the Zero-TIG
+ * per-frame-pair hot path.  Plain pointers and sizes only: every pointer is a DEVICE
+ * pointer owned by the caller (torch tensors' data_ptr() in the Python host),
+ * `stream` is a cudaStream_t passed as void*.  Every function returns 0 on success or
+ * a non-zero code; zt_last_error() returns the message of the last failure on the
+ * calling thread.  There is no CPU fallback: without a CUDA device every compute
+ * entry point fails.
+ *
+ * The reference (L-Forster/Zero-TIG) has no native code and therefore no FFI of its
+ * own: each entry point below names the reference Python function
+ * (file:line under the upstream tree) whose torch ops it replaces.  The host-side
+ * binding is ctypes (zero-tig_b200/_lib.py); INTEGRATION.md shows the stub.
+ *
+ * Internal activation layout: NHWC fp32 ("pixel-major", channel stride `cs` >= C,
+ * cs % 4 == 0, base pointers 16-byte aligned).  Frame-level tensors that cross the
+ * reference's Python interface stay NCHW fp32 like the reference's.
+ */
+#ifndef ZEROTIG_H_
+#define ZEROTIG_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ZT_OK 0
+#define ZT_ERR_ARG 1
+#define ZT_ERR_CUDA 2
+
+/* activation codes for ZtConv.act */
+#define ZT_ACT_NONE 0
+#define ZT_ACT_RELU 1
+#define ZT_ACT_LRELU02 2
+#define ZT_ACT_SIGMOID 3
+#define ZT_ACT_TANH 4
+
+/* epilogue codes for ZtConv.epi */
+#define ZT_EPI_PLAIN 0        /* out = scale * act(conv + bias)                                   */
+#define ZT_EPI_GRU_ZR 1       /* cout = 2*Ch: n<Ch  -> aux1[n]   = sigmoid(v)      (z gate)       */
+                              /*              n>=Ch -> out[n-Ch] = sigmoid(v)*aux0[n-Ch] (r*h)    */
+#define ZT_EPI_GRU_Q 2        /* q=tanh(v); out[n] = (1-z)*h + z*q with h=aux0[n], z=aux1[n]      */
+#define ZT_EPI_ADD_RELU 3     /* out = relu(aux0[n] + act(v))   (ResidualBlock tail)              */
+#define ZT_EPI_ADD 4          /* out = aux0[n] + act(v)         (Enhancer block)                  */
+
+const char* zt_last_error(void);
+int zt_version(void);
+/* number of kernel launches issued through this library since load (bench's gpu_launches) */
+int64_t zt_launch_count(void);
+
+/* ---- generic implicit-GEMM convolution, fp32 CUDA-core path --------------------------------
+ * Replaces every nn.Conv2d on the RAFT side (model/RAFT/extractor.py:9-10,44,131,140;
+ * update.py:9-10,36-42,82-86,122-125) and, in the fp32 build, the enhancement nets
+ * (model/model.py:20-22,36-38,54-71).  Input channels may come from two sources
+ * (virtual torch.cat([in0, in1], 1), update.py:47,50,130).  Weight layout
+ * [kh][kw][cin][w_cs] with w_cs = cout rounded up to 4 (zero padded). */
+typedef struct ZtConv {
+  const float* in0; int in0_cs; int c0;
+  const float* in1; int in1_cs; int c1;
+  const float* weight; int w_cs;
+  const float* bias;               /* [cout] or NULL */
+  float* out; int out_cs;
+  int B, H, W, Ho, Wo, cout;
+  int kh, kw, sh, sw, ph, pw;
+  int act; float out_scale; int epi;
+  const float* aux0; int aux0_cs;
+  float* aux1; int aux1_cs;
+} ZtConv;
+int zt_conv2d_nhwc_f32(const ZtConv* d, void* stream);
+
+/* ---- InstanceNorm2d (affine=False, eps) on NHWC fp32; extractor.py:27-31,129 -------------
+ * stats: per (image, channel) sums in fp64 scratch `stats` [B][C][2] (zeroed inside).
+ * apply: y = norm(x); if relu_inner y=relu(y); if res: y = res + y; if relu_outer y=relu(y) */
+int zt_instnorm_nhwc_f32(const float* x, int x_cs, float* out, int out_cs,
+                         const float* res, int res_cs, double* stats,
+                         int B, int HW, int C, float eps, int relu_inner, int relu_outer,
+                         void* stream);
+
+/* ---- RAFT correlation: corr.py:13-27,52-60 ---------------------------------------------- */
+/* out[c][r] = in[r][c]; out row stride out_rs (>= R) */
+int zt_transpose_f32(const float* in, int R, int C, int in_rs, float* out, int out_rs, void* stream);
+/* F.avg_pool2d(x,2,stride=2) over `planes` planes of h x w -> (h/2) x (w/2)  (corr.py:26) */
+int zt_avgpool2_f32(const float* in, float* out, int64_t planes, int h, int w, void* stream);
+/* CorrBlock.__call__ (corr.py:29-50) + bilinear_sampler (utils/utils.py:285-299):
+ * coords [N][2] (x,y), pyramid level l is [N][hl][wl]; out [N][out_cs], channel
+ * l*81 + a*9 + b samples level l at (x/2^l + a-4, y/2^l + b-4)  (x-offset major). */
+int zt_corr_lookup_f32(const float* l0, const float* l1, const float* l2, const float* l3,
+                       const int* hs, const int* ws_, /* host arrays[4] */
+                       const float* coords, float* out, int out_cs, int N, void* stream);
+/* RAFT.upsample_flow (raft.py:64-75): flow [N][flow_cs] NHWC (first 2 channels), mask [N][576]
+ * NHWC -> out NCHW [2][8h][8w] */
+int zt_convex_upsample_f32(const float* flow, int flow_cs, const float* mask, int mask_cs, float* out,
+                           int h8, int w8, void* stream);
+/* coords1 += delta (raft.py:120) and flow = coords1 - coords0 (raft.py:115) written into a
+ * channel slice; delta [N][d_cs], coords [N][2], flow_out [N][f_cs] (first 2 channels) */
+int zt_flow_update_f32(float* coords1, const float* delta, int d_cs, float* flow_out, int f_cs,
+                       float* flow_out2, int f2_cs, int h8, int w8, void* stream);
+
+/* ---- update_cache pre-processing: model/model.py:346-360 -------------------------------- */
+/* F.interpolate(bilinear, align_corners=False) of an NCHW 3-plane image to (ht,wd), *255.
+ * mode 0: write RAFT image1: replicate-pad to (hp,wp) (raft.py:132-138), 2*(v/255)-1,
+ *         NHWC cs=4 (4th channel 0) into out_f32.
+ * mode 1: truncate to uint8 into out_u8 [3][ht][wd] and accumulate hist [3][256] (int32,
+ *         zeroed inside). */
+int zt_resize255_f32(const float* img, int H, int W, int ht, int wd, int mode,
+                     float* out_f32, int hp, int wp, uint8_t* out_u8, int* hist, void* stream);
+/* torchvision equalize LUT (_functional_tensor._scale_channel): hist [3][256] -> lut [3][256] u8 */
+int zt_equalize_lut(const int* hist, uint8_t* lut, void* stream);
+/* apply LUT, then RAFT image2 packing as mode 0 above; optionally also writes the equalised
+ * u8 image (eq_u8 may be NULL) */
+int zt_equalize_apply_pack(const uint8_t* q, const uint8_t* lut, int ht, int wd, int hp, int wp,
+                           float* out_f32, uint8_t* eq_u8, void* stream);
+
+/* ---- warp: utils/utils.py:203-230, called twice with the same flow (model.py:374-375) ---
+ * flow NCHW [2][hf][wf]; img_a,img_b NCHW [C][H][W]; out_a,out_b same.  img_b/out_b may be
+ * NULL (single warp). */
+int zt_warp_pair_f32(const float* flow, int hf, int wf, const float* img_a, const float* img_b,
+                     float* out_a, float* out_b, int C, int H, int W, void* stream);
+
+/* ---- layout + Retinex elementwise: model/model.py:313-335 -------------------------------- */
+/* concat up to 4 NCHW sources (c channels each) into NHWC [HW][cs]; channels beyond the
+ * concatenation are zero; `add` is added to every source value (input + 1e-4, model.py:314) */
+int zt_pack_nhwc_f32(const float* s0, const float* s1, const float* s2, const float* s3,
+                     int c_each, int nsrc, float add, float* out, int cs, int64_t HW, void* stream);
+/* L2 = clamp((x+eps) - d, eps, 1): x NCHW [3], d NHWC (cs), L2 NCHW   (model.py:315-316) */
+int zt_retinex_l2_f32(const float* x, const float* d, int d_cs, float* L2, int64_t HW, float eps,
+                      void* stream);
+/* s2 = clamp(s, 1e-4, 1) (model.py:79); H2 = clamp((x+eps)/s2, eps, 1) (model.py:327-328);
+ * s NHWC (cs) already sigmoid'ed; outputs NCHW */
+int zt_retinex_h2_f32(const float* x, const float* s, int s_cs, float* s2, float* H2, int64_t HW,
+                      float eps, void* stream);
+/* H3 = clamp(H2 - d[0:3], eps, 1), s3 = clamp(s2 - d[3:6], eps, 1)  (model.py:334-337) */
+int zt_retinex_h5_f32(const float* H2, const float* s2, const float* d, int d_cs, float* H3,
+                      float* s3, int64_t HW, float eps, void* stream);
+/* save_images quantisation, predict.py:57-61: clip(x*255,0,255) -> uint8 (truncate), HWC */
+int zt_quantize_u8_hwc(const float* x, uint8_t* out, int C, int64_t HW, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZEROTIG_H_ */

@@ -1,0 +1,84 @@
+"""ctypes binding of libzerotig.so (the C ABI declared in include/zerotig.h).
+
+There is deliberately no fallback: if the library is missing or a call fails, a
+RuntimeError is raised.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libzerotig.so")
+
+c_fp = C.c_void_p  # device pointers travel as integers
+
+
+class ZtConv(C.Structure):
+    _fields_ = [
+        ("in0", c_fp), ("in0_cs", C.c_int), ("c0", C.c_int),
+        ("in1", c_fp), ("in1_cs", C.c_int), ("c1", C.c_int),
+        ("weight", c_fp), ("w_cs", C.c_int),
+        ("bias", c_fp),
+        ("out", c_fp), ("out_cs", C.c_int),
+        ("B", C.c_int), ("H", C.c_int), ("W", C.c_int), ("Ho", C.c_int), ("Wo", C.c_int), ("cout", C.c_int),
+        ("kh", C.c_int), ("kw", C.c_int), ("sh", C.c_int), ("sw", C.c_int), ("ph", C.c_int), ("pw", C.c_int),
+        ("act", C.c_int), ("out_scale", C.c_float), ("epi", C.c_int),
+        ("aux0", c_fp), ("aux0_cs", C.c_int),
+        ("aux1", c_fp), ("aux1_cs", C.c_int),
+    ]
+
+
+I, L, F, P = C.c_int, C.c_int64, C.c_float, C.c_void_p
+IP = C.POINTER(C.c_int)
+
+# name -> argtypes; every function returns int unless listed in _RESTYPE
+SIGNATURES = {
+    "zt_conv2d_nhwc_f32": [C.POINTER(ZtConv), P],
+    "zt_instnorm_nhwc_f32": [P, I, P, I, P, I, P, I, I, I, F, I, I, P],
+    "zt_transpose_f32": [P, I, I, I, P, I, P],
+    "zt_avgpool2_f32": [P, P, L, I, I, P],
+    "zt_corr_lookup_f32": [P, P, P, P, IP, IP, P, P, I, I, P],
+    "zt_convex_upsample_f32": [P, I, P, I, P, I, I, P],
+    "zt_flow_update_f32": [P, P, I, P, I, P, I, I, I, P],
+    "zt_resize255_f32": [P, I, I, I, I, I, P, I, I, P, P, P],
+    "zt_equalize_lut": [P, P, P],
+    "zt_equalize_apply_pack": [P, P, I, I, I, I, P, P, P],
+    "zt_warp_pair_f32": [P, I, I, P, P, P, P, I, I, I, P],
+    "zt_pack_nhwc_f32": [P, P, P, P, I, I, F, P, I, L, P],
+    "zt_retinex_l2_f32": [P, P, I, P, L, F, P],
+    "zt_retinex_h2_f32": [P, P, I, P, P, L, F, P],
+    "zt_retinex_h5_f32": [P, P, P, I, P, P, L, F, P],
+    "zt_quantize_u8_hwc": [P, P, I, L, P],
+    "zt_last_error": [],
+    "zt_version": [],
+    "zt_launch_count": [],
+}
+_RESTYPE = {"zt_last_error": C.c_char_p, "zt_launch_count": C.c_int64}
+
+_lib = None
+
+
+def lib():
+    """Load (once) and return the ctypes handle; raises if the library is not built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                "libzerotig.so is not built (%s). Run `python -m zero_tig_b200.build` "
+                "(needs nvcc); there is no CPU fallback." % LIB_PATH)
+        h = C.CDLL(LIB_PATH)
+        for name, args in SIGNATURES.items():
+            fn = getattr(h, name)  # AttributeError if the symbol is missing
+            fn.argtypes = args
+            fn.restype = _RESTYPE.get(name, C.c_int)
+        _lib = h
+    return _lib
+
+
+def check(rc, what=""):
+    if rc != 0:
+        msg = lib().zt_last_error()
+        raise RuntimeError("libzerotig %s failed (code %d): %s" % (what, rc, msg.decode() if msg else "?"))
+
+
+def launch_count():
+    return int(lib().zt_launch_count())

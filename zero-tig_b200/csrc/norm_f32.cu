@@ -1,0 +1,106 @@
+// InstanceNorm2d (affine=False, track_running_stats=False) on NHWC fp32.
+// Reference: nn.InstanceNorm2d in model/RAFT/extractor.py:27-31,129 (fnet only).
+// Two kernels: per-(image,channel) sum / sum-of-squares accumulated in fp64 (one pass,
+// no cancellation problem), then a fused normalise [+relu] [+residual] [+relu] pass.
+#include <algorithm>
+#include "common.cuh"
+
+namespace zt {
+
+// grid: (slabs, B); block: 256 threads; thread -> channel group of 4 (float4), strided pixels
+__global__ void __launch_bounds__(256) instnorm_stats_kernel(const float* __restrict__ x, int x_cs,
+                                                             double* __restrict__ stats, int HW, int C,
+                                                             int pix_per_block) {
+  const int c4n = C >> 2;                 // float4 groups per pixel
+  const int lanes = 256 / c4n;            // pixels processed concurrently
+  const int cg = threadIdx.x % c4n;
+  const int pl = threadIdx.x / c4n;
+  const int b = blockIdx.y;
+  const int p0 = blockIdx.x * pix_per_block;
+  const int p1 = min(p0 + pix_per_block, HW);
+  double s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
+  if (pl < lanes) {
+    const float* base = x + (int64_t)b * HW * x_cs + cg * 4;
+    for (int p = p0 + pl; p < p1; p += lanes) {
+      const float4 v = __ldg(reinterpret_cast<const float4*>(base + (int64_t)p * x_cs));
+      s[0] += v.x; q[0] += (double)v.x * v.x;
+      s[1] += v.y; q[1] += (double)v.y * v.y;
+      s[2] += v.z; q[2] += (double)v.z * v.z;
+      s[3] += v.w; q[3] += (double)v.w * v.w;
+    }
+  }
+  __shared__ double red[256][8];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) { red[threadIdx.x][e] = s[e]; red[threadIdx.x][4 + e] = q[e]; }
+  __syncthreads();
+  // threads 0..c4n-1 reduce over pixel lanes for their channel group
+  if (threadIdx.x < c4n) {
+    double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int l = 0; l < lanes; ++l)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] += red[l * c4n + threadIdx.x][e];
+    double* dst = stats + ((int64_t)b * C + threadIdx.x * 4) * 2;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      atomicAdd(dst + e * 2 + 0, acc[e]);
+      atomicAdd(dst + e * 2 + 1, acc[4 + e]);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) instnorm_apply_kernel(const float* __restrict__ x, int x_cs,
+                                                             float* __restrict__ out, int out_cs,
+                                                             const float* __restrict__ res, int res_cs,
+                                                             const double* __restrict__ stats, int HW, int C,
+                                                             float eps, int relu_inner, int relu_outer,
+                                                             int64_t total4) {
+  const int c4n = C >> 2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % c4n);
+    const int64_t pix = i / c4n;          // b*HW + p
+    const int b = (int)(pix / HW);
+    const double* st = stats + ((int64_t)b * C + cg * 4) * 2;
+    float4 v = __ldg(reinterpret_cast<const float4*>(x + pix * x_cs + cg * 4));
+    float r[4] = {v.x, v.y, v.z, v.w};
+    float4 rv = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (res) rv = __ldg(reinterpret_cast<const float4*>(res + pix * res_cs + cg * 4));
+    const float rr[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const double mean = st[e * 2] / HW;
+      double var = st[e * 2 + 1] / HW - mean * mean;   // biased variance
+      var = var < 0 ? 0 : var;
+      const float rstd = (float)(1.0 / sqrt(var + (double)eps));
+      float y = (r[e] - (float)mean) * rstd;
+      if (relu_inner) y = fmaxf(y, 0.f);
+      if (res) y += rr[e];
+      if (relu_outer) y = fmaxf(y, 0.f);
+      r[e] = y;
+    }
+    *reinterpret_cast<float4*>(out + pix * out_cs + cg * 4) = make_float4(r[0], r[1], r[2], r[3]);
+  }
+}
+
+}  // namespace zt
+
+extern "C" int zt_instnorm_nhwc_f32(const float* x, int x_cs, float* out, int out_cs, const float* res,
+                                    int res_cs, double* stats, int B, int HW, int C, float eps,
+                                    int relu_inner, int relu_outer, void* stream) {
+  using namespace zt;
+  ZT_REQUIRE(x && out && stats, "instnorm: null pointer");
+  ZT_REQUIRE((C & 3) == 0 && C <= 1024 && (x_cs & 3) == 0 && (out_cs & 3) == 0 && (!res || (res_cs & 3) == 0),
+             "instnorm: C and strides must be multiples of 4 (C=%d)", C);
+  ZT_REQUIRE(B > 0 && HW > 0, "instnorm: bad dims");
+  cudaStream_t st = (cudaStream_t)stream;
+  ZT_CUDA(cudaMemsetAsync(stats, 0, sizeof(double) * 2 * B * C, st));
+  const int slabs = max(1, min(ceil_div(HW, 64), (4 * kNumSMs) / B));
+  const int ppb = ceil_div(HW, slabs);
+  instnorm_stats_kernel<<<dim3(ceil_div(HW, ppb), B), 256, 0, st>>>(x, x_cs, stats, HW, C, ppb);
+  if (int e = check_launch("instnorm_stats_kernel")) return e;
+  const int64_t total4 = (int64_t)B * HW * (C >> 2);
+  const int blocks = (int)std::min<int64_t>(ceil_div64(total4, 256), 8 * kNumSMs);
+  instnorm_apply_kernel<<<blocks, 256, 0, st>>>(x, x_cs, out, out_cs, res, res_cs, stats, HW, C, eps,
+                                                relu_inner, relu_outer, total4);
+  return check_launch("instnorm_apply_kernel");
+}

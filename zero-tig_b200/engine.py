@@ -1,0 +1,372 @@
+"""Host-side orchestration of the sm_100a kernels: RAFT, update_cache, Retinex nets.
+
+The engines read parameters from the (reference-compatible) nn.Module containers,
+re-layout them once per device / parameter version, own the NHWC workspaces and issue
+the kernel sequence on torch's current stream.  Nothing here computes on the CPU.
+"""
+import torch
+
+from . import ops
+from .ops import ConvW
+
+
+def _dev_check(t):
+    if not t.is_cuda:
+        raise RuntimeError("zero_tig_b200 runs on CUDA only (no CPU fallback); got a %s tensor" % t.device)
+
+
+class _Workspace:
+    """Named scratch tensors, allocated on first use per shape and kept (180 GB of HBM)."""
+
+    def __init__(self, device):
+        self.device = device
+        self.bufs = {}
+
+    def get(self, name, shape, dtype=torch.float32, zero=False):
+        key = (name, tuple(shape), dtype)
+        t = self.bufs.get(key)
+        if t is None:
+            t = (torch.zeros if zero else torch.empty)(shape, device=self.device, dtype=dtype)
+            self.bufs[key] = t
+        return t
+
+
+def _param_version(module):
+    return tuple((p.data_ptr(), p._version) for p in list(module.parameters()) + list(module.buffers()))
+
+
+# ----------------------------------------------------------------------------------------
+# RAFT
+# ----------------------------------------------------------------------------------------
+class RaftEngine:
+    """RAFT.forward (model/RAFT/raft.py:77-130) on the kernels in csrc/."""
+
+    def __init__(self, raft):
+        self.raft = raft
+        self._wkey = None
+        self.w = None
+        self.ws = None
+
+    # ---- weights ----
+    def _prepare(self, device):
+        key = (str(device), _param_version(self.raft))
+        if key == self._wkey:
+            return
+        sd = {k: v.detach().to(device) for k, v in self.raft.state_dict().items()}
+        w = {}
+
+        def bn(prefix):
+            return (sd[prefix + ".weight"], sd[prefix + ".bias"], sd[prefix + ".running_mean"],
+                    sd[prefix + ".running_var"])
+
+        for enc, is_bn in (("fnet", False), ("cnet", True)):
+            w[f"{enc}.conv1"] = ConvW(sd[f"{enc}.conv1.weight"], sd[f"{enc}.conv1.bias"], cin_pad=4,
+                                      bn=bn(f"{enc}.norm1") if is_bn else None)
+            for li in (1, 2, 3):
+                for bi in (0, 1):
+                    p = f"{enc}.layer{li}.{bi}"
+                    w[p + ".conv1"] = ConvW(sd[p + ".conv1.weight"], sd[p + ".conv1.bias"],
+                                            bn=bn(p + ".norm1") if is_bn else None)
+                    w[p + ".conv2"] = ConvW(sd[p + ".conv2.weight"], sd[p + ".conv2.bias"],
+                                            bn=bn(p + ".norm2") if is_bn else None)
+                    if p + ".downsample.0.weight" in sd:
+                        w[p + ".down"] = ConvW(sd[p + ".downsample.0.weight"], sd[p + ".downsample.0.bias"],
+                                               bn=bn(p + ".norm3") if is_bn else None)
+        w["fnet.conv2"] = ConvW(sd["fnet.conv2.weight"], sd["fnet.conv2.bias"])
+        w["cnet.conv2.net"] = ConvW(sd["cnet.conv2.weight"], sd["cnet.conv2.bias"], out_slice=slice(0, 128))
+        w["cnet.conv2.inp"] = ConvW(sd["cnet.conv2.weight"], sd["cnet.conv2.bias"], out_slice=slice(128, 256))
+        u = "update_block."
+        for name in ("convc1", "convc2", "convf2", "conv"):
+            w["enc." + name] = ConvW(sd[u + f"encoder.{name}.weight"], sd[u + f"encoder.{name}.bias"])
+        w["enc.convf1"] = ConvW(sd[u + "encoder.convf1.weight"], sd[u + "encoder.convf1.bias"], cin_pad=4)
+        for s in ("1", "2"):
+            wz, wr = sd[u + f"gru.convz{s}.weight"], sd[u + f"gru.convr{s}.weight"]
+            bz, br = sd[u + f"gru.convz{s}.bias"], sd[u + f"gru.convr{s}.bias"]
+            w["gru.zr" + s] = ConvW(torch.cat([wz, wr], 0), torch.cat([bz, br], 0))
+            w["gru.q" + s] = ConvW(sd[u + f"gru.convq{s}.weight"], sd[u + f"gru.convq{s}.bias"])
+        w["fh1"] = ConvW(sd[u + "flow_head.conv1.weight"], sd[u + "flow_head.conv1.bias"])
+        w["fh2"] = ConvW(sd[u + "flow_head.conv2.weight"], sd[u + "flow_head.conv2.bias"])
+        w["mask0"] = ConvW(sd[u + "mask.0.weight"], sd[u + "mask.0.bias"])
+        w["mask2"] = ConvW(sd[u + "mask.2.weight"], sd[u + "mask.2.bias"])
+        self.w, self._wkey = w, key
+        if self.ws is None or self.ws.device != device:
+            self.ws = _Workspace(device)
+
+    # ---- encoders (extractor.py:167-191) ----
+    def _encoder(self, enc, x, B, H, W, is_bn):
+        w, ws = self.w, self.ws
+        stats = ws.get("in_stats", (B * 128 * 2,), torch.float64)
+        h, wd = H // 2, W // 2
+
+        def buf(tag, hh, ww, c):
+            return ws.get(f"{enc}.{tag}", (B * hh * ww, c))
+
+        y = buf("stem", h, wd, 64)
+        ops.conv2d(w[enc + ".conv1"], x, 4, 4, B, H, W, y, 64, stride=2, pad=(3, 3), act="relu" if is_bn else "none")
+        if not is_bn:
+            ops.instnorm(y, 64, y, 64, stats, B, h * wd, 64, relu_inner=True)
+        cin = 64
+        for li, (cout, stride) in enumerate(((64, 1), (96, 2), (128, 2)), start=1):
+            for bi in (0, 1):
+                s = stride if bi == 0 else 1
+                p = f"{enc}.layer{li}.{bi}"
+                ho, wo = h // s if s == 1 else (h + 2 - 3) // s + 1, wd // s if s == 1 else (wd + 2 - 3) // s + 1
+                t1 = buf(f"l{li}b{bi}.t1", ho, wo, cout)
+                ops.conv2d(w[p + ".conv1"], y, cin, cin, B, h, wd, t1, cout, stride=s, pad=(1, 1),
+                           act="relu" if is_bn else "none")
+                if not is_bn:
+                    ops.instnorm(t1, cout, t1, cout, stats, B, ho * wo, cout, relu_inner=True)
+                sc = y
+                if s != 1:
+                    sc = buf(f"l{li}b{bi}.sc", ho, wo, cout)
+                    ops.conv2d(w[p + ".down"], y, cin, cin, B, h, wd, sc, cout, stride=s, pad=(0, 0))
+                    if not is_bn:
+                        ops.instnorm(sc, cout, sc, cout, stats, B, ho * wo, cout, relu_inner=False)
+                out = buf(f"l{li}b{bi}.out", ho, wo, cout)
+                if is_bn:
+                    ops.conv2d(w[p + ".conv2"], t1, cout, cout, B, ho, wo, out, cout, pad=(1, 1), act="relu",
+                               epi="add_relu", aux0=sc, aux0_cs=cout)
+                else:
+                    t2 = buf(f"l{li}b{bi}.t2", ho, wo, cout)
+                    ops.conv2d(w[p + ".conv2"], t1, cout, cout, B, ho, wo, t2, cout, pad=(1, 1))
+                    ops.instnorm(t2, cout, out, cout, stats, B, ho * wo, cout, relu_inner=True, relu_outer=True,
+                                 res=sc, res_cs=cout)
+                y, cin, h, wd = out, cout, ho, wo
+        return y, h, wd
+
+    # ---- full forward on packed inputs ----
+    def forward_packed(self, x2, hp, wp, iters=12):
+        """x2: [2][hp][wp][4] fp32 NHWC (image1, image2 normalised to [-1,1], padded).
+        Returns flow_up NCHW [1,2,hp,wp] (a workspace tensor, valid until the next call)."""
+        _dev_check(x2)
+        self._prepare(x2.device)
+        w, ws = self.w, self.ws
+        assert hp % 8 == 0 and wp % 8 == 0
+        h8, w8 = hp // 8, wp // 8
+        N = h8 * w8
+        # feature network on both images
+        f, fh, fw = self._encoder("fnet", x2, 2, hp, wp, False)
+        assert (fh, fw) == (h8, w8)
+        fmap = ws.get("fmap", (2 * N, 256))
+        ops.conv2d(w["fnet.conv2"], f, 128, 128, 2, h8, w8, fmap, 256)
+        # all-pairs correlation volume + pyramid (corr.py:13-27,52-60)
+        N4 = (N + 3) // 4 * 4
+        f2t = ws.get("f2t", (256, N4))
+        ops.transpose(fmap[N:], N, 256, 256, f2t, N4)
+        hs, wsz = [h8], [w8]
+        for _ in range(3):
+            hs.append(hs[-1] // 2)
+            wsz.append(wsz[-1] // 2)
+        if hs[3] < 2 or wsz[3] < 2:
+            raise RuntimeError("RAFT grid %dx%d is too small: the reference's 4-level lookup yields NaN when the "
+                               "coarsest level is below 2x2 (needs a feature grid >= 16x16)" % (h8, w8))
+        lv = [ws.get(f"corr{i}", (N, hs[i] * wsz[i])) for i in range(4)]
+        cw = ConvW.__new__(ConvW)
+        cw.w, cw.b, cw.kh, cw.kw, cw.cin, cw.cout, cw.w_cs = f2t, None, 1, 1, 256, N, N4
+        ops.conv2d(cw, fmap, 256, 256, 1, h8, w8, lv[0], N, scale=0.0625)
+        for i in range(3):
+            ops.avgpool2(lv[i], lv[i + 1], N, hs[i], wsz[i])
+        # context network
+        c, ch, cwid = self._encoder("cnet", x2, 1, hp, wp, True)
+        hx = ws.get("hx", (N, 384))
+        ops.conv2d(w["cnet.conv2.net"], c, 128, 128, 1, h8, w8, hx, 384, act="tanh")
+        ops.conv2d(w["cnet.conv2.inp"], c, 128, 128, 1, h8, w8, hx, 384, out_off=128, act="relu")
+        # iteration state
+        grid = ws.bufs.get(("grid", h8, w8))
+        if grid is None:
+            ys, xs = torch.meshgrid(torch.arange(h8, device=x2.device), torch.arange(w8, device=x2.device),
+                                    indexing="ij")
+            grid = torch.stack([xs, ys], -1).float().reshape(N, 2).contiguous()
+            ws.bufs[("grid", h8, w8)] = grid
+        coords1 = ws.get("coords1", (N, 2))
+        coords1.copy_(grid)
+        flow4 = ws.get("flow4", (N, 4), zero=True)
+        corr = ws.get("corrfeat", (N, 324))
+        c1 = ws.get("c1", (N, 256))
+        c2f = ws.get("c2f", (N, 256))
+        f1 = ws.get("f1", (N, 128))
+        z = ws.get("z", (N, 128))
+        rh = ws.get("rh", (N, 128))
+        fhid = ws.get("fhid", (N, 256))
+        delta = ws.get("delta", (N, 4), zero=True)
+        ops.flow_update(coords1, None, 0, flow4, 4, hx, 384, 382, h8, w8)
+        for it in range(iters):
+            ops.corr_lookup(lv, hs, wsz, coords1, corr, 324, N)
+            ops.conv2d(w["enc.convc1"], corr, 324, 324, 1, h8, w8, c1, 256, act="relu")
+            ops.conv2d(w["enc.convc2"], c1, 256, 256, 1, h8, w8, c2f, 256, pad=(1, 1), act="relu")
+            ops.conv2d(w["enc.convf1"], flow4, 4, 4, 1, h8, w8, f1, 128, pad=(3, 3), act="relu")
+            ops.conv2d(w["enc.convf2"], f1, 128, 128, 1, h8, w8, c2f, 256, out_off=192, pad=(1, 1), act="relu")
+            ops.conv2d(w["enc.conv"], c2f, 256, 256, 1, h8, w8, hx, 384, out_off=256, pad=(1, 1), act="relu")
+            for s, pad in (("1", (0, 2)), ("2", (2, 0))):
+                ops.conv2d(w["gru.zr" + s], hx, 384, 384, 1, h8, w8, rh, 128, pad=pad, epi="gru_zr",
+                           aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128)
+                ops.conv2d(w["gru.q" + s], rh, 128, 128, 1, h8, w8, hx, 384, in1=hx, in1_cs=384, c1=256,
+                           in1_off=128, pad=pad, epi="gru_q", aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128)
+            ops.conv2d(w["fh1"], hx, 384, 128, 1, h8, w8, fhid, 256, pad=(1, 1), act="relu")
+            ops.conv2d(w["fh2"], fhid, 256, 256, 1, h8, w8, delta, 4, pad=(1, 1))
+            ops.flow_update(coords1, delta, 4, flow4, 4, hx, 384, 382, h8, w8)
+        # convex upsampling mask only for the returned (last) prediction (raft.py:122-130, Q15)
+        mh = ws.get("maskh", (N, 256))
+        mask = ws.get("mask", (N, 576))
+        ops.conv2d(w["mask0"], hx, 384, 128, 1, h8, w8, mh, 256, pad=(1, 1), act="relu")
+        ops.conv2d(w["mask2"], mh, 256, 256, 1, h8, w8, mask, 576, scale=0.25)
+        flow_up = ws.get("flow_up", (1, 2, hp, wp))
+        ops.convex_upsample(flow4, 4, mask, 576, flow_up, h8, w8)
+        self.last = dict(fmap=fmap, levels=lv, hs=hs, ws=wsz, flow4=flow4, hx=hx, corr=corr, N=N, h8=h8, w8=w8)
+        return flow_up
+
+    def forward(self, image1, image2, iters=12):
+        """API-compatible RAFT.forward on NCHW [1,3,H,W] images in 0..255 (raft.py:77-130).
+        Input padding / normalisation / packing use torch device ops here; the per-frame hot
+        path (update_cache) uses the fused kernels instead."""
+        _dev_check(image1)
+        import torch.nn.functional as F
+        assert image1.shape[0] == 1, "batch 1 only (the reference CLIs use batch 1)"
+        ht, wd = image1.shape[-2:]
+        ph, pw = (((ht // 8) + 1) * 8 - ht) % 8, (((wd // 8) + 1) * 8 - wd) % 8
+        pad = [pw // 2, pw - pw // 2, ph // 2, ph - ph // 2]
+        x = torch.cat([image1, image2], 0).float()
+        x = F.pad(x, pad, mode="replicate")
+        x = 2 * (x / 255.0) - 1.0
+        x = F.pad(x.permute(0, 2, 3, 1), [0, 1]).contiguous()
+        hp, wp = ht + ph, wd + pw
+        flow_up = self.forward_packed(x, hp, wp, iters).clone()
+        flow_low = self.last["flow4"][:, :2].reshape(1, self.last["h8"], self.last["w8"], 2).permute(0, 3, 1, 2)
+        return flow_low.contiguous(), flow_up
+
+
+# ----------------------------------------------------------------------------------------
+# Retinex nets + update_cache
+# ----------------------------------------------------------------------------------------
+class FrameEngine:
+    """Finetunemodel.forward / update_cache (model/model.py:312-384) on the kernels."""
+
+    EPS = 1e-4
+
+    def __init__(self, model):
+        self.model = model
+        self._wkey = None
+        self.ws = None
+
+    def _prepare(self, device):
+        m = self.model
+        key = (str(device), _param_version(m.enhance), _param_version(m.denoise_1), _param_version(m.denoise_2))
+        if key == self._wkey:
+            return
+        w = {}
+        for n, d, cin_pad in (("d1", m.denoise_1, 4), ("d2", m.denoise_2, 12)):
+            w[n + ".c1"] = ConvW(d.conv1.weight.to(device), d.conv1.bias.to(device), cin_pad=cin_pad)
+            w[n + ".c2"] = ConvW(d.conv2.weight.to(device), d.conv2.bias.to(device))
+            w[n + ".c3"] = ConvW(d.conv3.weight.to(device), d.conv3.bias.to(device))
+        e = m.enhance
+        w["e.in"] = ConvW(e.in_conv[0].weight.to(device), e.in_conv[0].bias.to(device), cin_pad=12)
+        bnm = e.conv[1]
+        w["e.blk"] = ConvW(e.conv[0].weight.to(device), e.conv[0].bias.to(device),
+                           bn=(bnm.weight.to(device), bnm.bias.to(device), bnm.running_mean.to(device),
+                               bnm.running_var.to(device)), eps=bnm.eps)
+        w["e.out"] = ConvW(e.out_conv[0].weight.to(device), e.out_conv[0].bias.to(device))
+        self.w, self._wkey = w, key
+        if self.ws is None or self.ws.device != device:
+            self.ws = _Workspace(device)
+
+    # ---- nets ----
+    def denoise1_L2(self, x, H, W):
+        """L2 = clamp((x+eps) - denoise_1(x+eps), eps, 1)   (model.py:313-316)."""
+        w, ws, HW = self.w, self.ws, H * W
+        xp = ws.get("xp", (HW, 4))
+        a1 = ws.get("a48a", (HW, 48))
+        a2 = ws.get("a48b", (HW, 48))
+        d = ws.get("d4", (HW, 4))
+        ops.pack_nhwc([x], 3, self.EPS, xp, 4, HW)
+        ops.conv2d(w["d1.c1"], xp, 4, 4, 1, H, W, a1, 48, pad=(1, 1), act="lrelu")
+        ops.conv2d(w["d1.c2"], a1, 48, 48, 1, H, W, a2, 48, pad=(1, 1), act="lrelu")
+        ops.conv2d(w["d1.c3"], a2, 48, 48, 1, H, W, d, 4)
+        L2 = torch.empty_like(x)
+        ops.retinex_l2(x, d, 4, L2, HW, self.EPS)
+        return L2
+
+    def enhance_H2(self, x, H3_wp, s3_wp, L2, H, W):
+        """s2 = enhance(cat[H3_wp, s3_wp, L2]); H2 = clamp((x+eps)/s2, eps, 1)  (model.py:326-328)."""
+        w, ws, HW = self.w, self.ws, H * W
+        ep = ws.get("ep12", (HW, 12))
+        fa = ws.get("f64a", (HW, 64))
+        fb = ws.get("f64b", (HW, 64))
+        s4 = ws.get("s4", (HW, 4))
+        ops.pack_nhwc([H3_wp, s3_wp, L2], 3, 0.0, ep, 12, HW)
+        ops.conv2d(w["e.in"], ep, 12, 12, 1, H, W, fa, 64, pad=(1, 1), act="relu")
+        cur, nxt = fa, fb
+        for _ in range(3):  # one shared conv+BN applied three times (model.py:60-67, Q5)
+            ops.conv2d(w["e.blk"], cur, 64, 64, 1, H, W, nxt, 64, pad=(1, 1), act="relu", epi="add",
+                       aux0=cur, aux0_cs=64)
+            cur, nxt = nxt, cur
+        ops.conv2d(w["e.out"], cur, 64, 64, 1, H, W, s4, 4, pad=(1, 1), act="sigmoid")
+        s2 = torch.empty_like(x)
+        H2 = torch.empty_like(x)
+        ops.retinex_h2(x, s4, 4, s2, H2, HW, self.EPS)
+        return s2, H2
+
+    def denoise2_H3(self, H3_wp, s3_wp, H2, s2, H, W):
+        """H5 = clamp(cat[H2,s2] - denoise_2(cat[H3_wp,s3_wp,H2,s2]), eps, 1)  (model.py:334-337)."""
+        w, ws, HW = self.w, self.ws, H * W
+        dp = ws.get("dp12", (HW, 12))
+        a1 = ws.get("a48a", (HW, 48))
+        a2 = ws.get("a48b", (HW, 48))
+        d = ws.get("d8", (HW, 8))
+        ops.pack_nhwc([H3_wp, s3_wp, H2, s2], 3, 0.0, dp, 12, HW)
+        ops.conv2d(w["d2.c1"], dp, 12, 12, 1, H, W, a1, 48, pad=(1, 1), act="lrelu")
+        ops.conv2d(w["d2.c2"], a1, 48, 48, 1, H, W, a2, 48, pad=(1, 1), act="lrelu")
+        ops.conv2d(w["d2.c3"], a2, 48, 48, 1, H, W, d, 8)
+        H3 = torch.empty_like(H2)
+        s3 = torch.empty_like(H2)
+        ops.retinex_h5(H2, s2, d, 8, H3, s3, HW, self.EPS)
+        return H3, s3
+
+    # ---- update_cache (model.py:346-384) ----
+    def raft_inputs(self, last_H3, L2, of_scale):
+        """Resize, *255, quantise+equalise image2, normalise, pad, pack -> [2][hp][wp][4]."""
+        ws = self.ws
+        H, W = last_H3.shape[-2:]
+        ht, wd = H // of_scale, W // of_scale
+        hp, wp = (ht + 7) // 8 * 8, (wd + 7) // 8 * 8
+        x2 = ws.get("raft_in", (2, hp, wp, 4))
+        q = ws.get("l2_u8", (3, ht, wd), torch.uint8)
+        hist = ws.get("hist", (768,), torch.int32)
+        lut = ws.get("lut", (768,), torch.uint8)
+        ops.resize255_image1(last_H3, H, W, ht, wd, x2[0], hp, wp)
+        ops.resize255_quant_hist(L2, H, W, ht, wd, q, hist)
+        ops.equalize_lut(hist, lut)
+        ops.equalize_apply_pack(q, lut, ht, wd, hp, wp, x2[1])
+        return x2, hp, wp
+
+    def update_cache(self, last_H3, last_s3, L2, of_scale):
+        for t in (last_H3, last_s3, L2):
+            _dev_check(t)
+        self._prepare(L2.device)
+        assert last_H3.shape[0] == 1 and last_H3.shape[1] == 3, "batch 1, 3 channels"
+        last_H3, last_s3, L2 = last_H3.contiguous(), last_s3.contiguous(), L2.contiguous()
+        H, W = last_H3.shape[-2:]
+        x2, hp, wp = self.raft_inputs(last_H3, L2, of_scale)
+        flow_up = self.model.raft.engine().forward_packed(x2, hp, wp, 12)
+        H3_wp = torch.empty_like(last_H3)
+        s3_wp = torch.empty_like(last_s3)
+        ops.warp_pair(flow_up, hp, wp, last_H3, last_s3, H3_wp, s3_wp, 3, H, W)
+        return H3_wp, s3_wp
+
+    # ---- Finetunemodel.forward (model.py:312-340) ----
+    def infer(self, x, is_new_seq, last_H3, last_s3, of_scale):
+        _dev_check(x)
+        assert x.dim() == 4 and x.shape[0] == 1 and x.shape[1] == 3, "expects [1,3,H,W] (the CLIs use batch 1)"
+        x = x.contiguous().float()
+        self._prepare(x.device)
+        H, W = x.shape[-2:]
+        L2 = self.denoise1_L2(x, H, W)
+        if is_new_seq:
+            zeros = self.ws.get("zeros3", (1, 3, H, W), zero=True)
+            H3_wp = s3_wp = zeros
+        else:
+            H3_wp, s3_wp = self.update_cache(last_H3, last_s3, L2, of_scale)
+        s2, H2 = self.enhance_H2(x, H3_wp, s3_wp, L2, H, W)
+        if is_new_seq:  # inference-only substitution (model.py:330-332, Q12)
+            H3_wp = s3_wp = H2
+        H3, s3 = self.denoise2_H3(H3_wp, s3_wp, H2, s2, H, W)
+        return dict(L2=L2, s2=s2, H2=H2, H3=H3, s3=s3, H3_wp=H3_wp, s3_wp=s3_wp)

@@ -1,0 +1,151 @@
+"""Thin torch-tensor wrappers over the libzerotig C ABI (include/zerotig.h).
+
+Each wrapper borrows ``data_ptr()``s for the duration of one call on torch's current
+CUDA stream; outputs are caller- or torch-allocated.  No wrapper has a CPU path: a
+non-CUDA tensor raises.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import ZtConv, check, lib
+
+ACT = {"none": 0, "relu": 1, "lrelu": 2, "sigmoid": 3, "tanh": 4}
+EPI = {"plain": 0, "gru_zr": 1, "gru_q": 2, "add_relu": 3, "add": 4}
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t, offset_elems=0):
+    """Device pointer (as c_void_p) of a float tensor, optionally offset by elements."""
+    if t is None:
+        return C.c_void_p(0)
+    if not t.is_cuda:
+        raise RuntimeError("zero_tig_b200 ops need CUDA tensors (no CPU fallback)")
+    return C.c_void_p(t.data_ptr() + offset_elems * t.element_size())
+
+
+class ConvW:
+    """A conv layer's parameters in kernel layout: weight [kh][kw][cin_pad][w_cs], bias [cout]."""
+    __slots__ = ("w", "b", "kh", "kw", "cin", "cout", "w_cs")
+
+    def __init__(self, weight, bias=None, cin_pad=None, bn=None, eps=1e-5, out_slice=None):
+        w = weight.detach().float()
+        b = None if bias is None else bias.detach().float()
+        if bn is not None:  # fold eval-mode BatchNorm: (gamma, beta, mean, var)
+            g, beta, mean, var = [t.detach().float() for t in bn]
+            s = g / torch.sqrt(var + eps)
+            w = w * s.view(-1, 1, 1, 1)
+            b0 = b if b is not None else torch.zeros_like(mean)
+            b = (b0 - mean) * s + beta
+        if out_slice is not None:
+            w = w[out_slice]
+            b = None if b is None else b[out_slice]
+        cout, cin, kh, kw = w.shape
+        cin_p = cin_pad or ((cin + 3) // 4 * 4)
+        w_cs = (cout + 3) // 4 * 4
+        wk = torch.zeros(kh, kw, cin_p, w_cs, device=w.device, dtype=torch.float32)
+        wk[:, :, :cin, :cout] = w.permute(2, 3, 1, 0)
+        self.w, self.b = wk.contiguous(), (None if b is None else b.contiguous())
+        self.kh, self.kw, self.cin, self.cout, self.w_cs = kh, kw, cin_p, cout, w_cs
+
+
+def conv2d(wt: ConvW, in0, in0_cs, c0, B, H, W, out, out_cs, *, in0_off=0, in1=None, in1_cs=0, c1=0,
+           in1_off=0, out_off=0, stride=1, pad=(0, 0), act="none", scale=1.0, epi="plain",
+           aux0=None, aux0_cs=0, aux0_off=0, aux1=None, aux1_cs=0, aux1_off=0):
+    """out[:, out_off:out_off+cout] = epilogue(conv(cat[in0[:, in0_off:+c0], in1[:, in1_off:+c1]]))."""
+    assert c0 + c1 == wt.cin, (c0, c1, wt.cin)
+    sh = sw = stride
+    ph, pw = pad
+    Ho = (H + 2 * ph - wt.kh) // sh + 1
+    Wo = (W + 2 * pw - wt.kw) // sw + 1
+    d = ZtConv()
+    d.in0, d.in0_cs, d.c0 = _p(in0, in0_off), in0_cs, c0
+    d.in1, d.in1_cs, d.c1 = _p(in1, in1_off), in1_cs, c1
+    d.weight, d.w_cs = _p(wt.w), wt.w_cs
+    d.bias = _p(wt.b)
+    d.out, d.out_cs = _p(out, out_off), out_cs
+    d.B, d.H, d.W, d.Ho, d.Wo, d.cout = B, H, W, Ho, Wo, wt.cout
+    d.kh, d.kw, d.sh, d.sw, d.ph, d.pw = wt.kh, wt.kw, sh, sw, ph, pw
+    d.act, d.out_scale, d.epi = ACT[act], scale, EPI[epi]
+    d.aux0, d.aux0_cs = _p(aux0, aux0_off), aux0_cs
+    d.aux1, d.aux1_cs = _p(aux1, aux1_off), aux1_cs
+    check(lib().zt_conv2d_nhwc_f32(C.byref(d), _stream()), "conv2d")
+    return Ho, Wo
+
+
+def instnorm(x, x_cs, out, out_cs, stats, B, HW, Cn, relu_inner, relu_outer=False, res=None, res_cs=0, eps=1e-5):
+    check(lib().zt_instnorm_nhwc_f32(_p(x), x_cs, _p(out), out_cs, _p(res), res_cs, _p(stats), B, HW, Cn,
+                                     eps, int(relu_inner), int(relu_outer), _stream()), "instnorm")
+
+
+def transpose(x, R, Cc, in_rs, out, out_rs):
+    check(lib().zt_transpose_f32(_p(x), R, Cc, in_rs, _p(out), out_rs, _stream()), "transpose")
+
+
+def avgpool2(x, out, planes, h, w):
+    check(lib().zt_avgpool2_f32(_p(x), _p(out), planes, h, w, _stream()), "avgpool2")
+
+
+def corr_lookup(levels, hs, ws, coords, out, out_cs, N):
+    IA = C.c_int * 4
+    check(lib().zt_corr_lookup_f32(_p(levels[0]), _p(levels[1]), _p(levels[2]), _p(levels[3]),
+                                   IA(*hs), IA(*ws), _p(coords), _p(out), out_cs, N, _stream()), "corr_lookup")
+
+
+def convex_upsample(flow, flow_cs, mask, mask_cs, out, h8, w8):
+    check(lib().zt_convex_upsample_f32(_p(flow), flow_cs, _p(mask), mask_cs, _p(out), h8, w8, _stream()),
+          "convex_upsample")
+
+
+def flow_update(coords1, delta, d_cs, f1, f1_cs, f2, f2_cs, f2_off, h8, w8):
+    check(lib().zt_flow_update_f32(_p(coords1), _p(delta), d_cs, _p(f1), f1_cs, _p(f2, f2_off), f2_cs, h8, w8,
+                                   _stream()), "flow_update")
+
+
+def resize255_image1(img, H, W, ht, wd, out, hp, wp):
+    check(lib().zt_resize255_f32(_p(img), H, W, ht, wd, 0, _p(out), hp, wp, None, None, _stream()), "resize255")
+
+
+def resize255_quant_hist(img, H, W, ht, wd, out_u8, hist):
+    check(lib().zt_resize255_f32(_p(img), H, W, ht, wd, 1, None, ht, wd, _p(out_u8), _p(hist), _stream()),
+          "resize255")
+
+
+def equalize_lut(hist, lut):
+    check(lib().zt_equalize_lut(_p(hist), _p(lut), _stream()), "equalize_lut")
+
+
+def equalize_apply_pack(q, lut, ht, wd, hp, wp, out, eq_u8=None):
+    check(lib().zt_equalize_apply_pack(_p(q), _p(lut), ht, wd, hp, wp, _p(out), _p(eq_u8), _stream()),
+          "equalize_apply_pack")
+
+
+def warp_pair(flow, hf, wf, img_a, img_b, out_a, out_b, Cn, H, W):
+    check(lib().zt_warp_pair_f32(_p(flow), hf, wf, _p(img_a), _p(img_b), _p(out_a), _p(out_b), Cn, H, W,
+                                 _stream()), "warp_pair")
+
+
+def pack_nhwc(srcs, c_each, add, out, cs, HW):
+    s = list(srcs) + [None] * (4 - len(srcs))
+    check(lib().zt_pack_nhwc_f32(_p(s[0]), _p(s[1]), _p(s[2]), _p(s[3]), c_each, len(srcs), add, _p(out), cs, HW,
+                                 _stream()), "pack_nhwc")
+
+
+def retinex_l2(x, d, d_cs, L2, HW, eps):
+    check(lib().zt_retinex_l2_f32(_p(x), _p(d), d_cs, _p(L2), HW, eps, _stream()), "retinex_l2")
+
+
+def retinex_h2(x, s, s_cs, s2, H2, HW, eps):
+    check(lib().zt_retinex_h2_f32(_p(x), _p(s), s_cs, _p(s2), _p(H2), HW, eps, _stream()), "retinex_h2")
+
+
+def retinex_h5(H2, s2, d, d_cs, H3, s3, HW, eps):
+    check(lib().zt_retinex_h5_f32(_p(H2), _p(s2), _p(d), d_cs, _p(H3), _p(s3), HW, eps, _stream()), "retinex_h5")
+
+
+def quantize_u8_hwc(x, out, Cn, HW):
+    check(lib().zt_quantize_u8_hwc(_p(x), _p(out), Cn, HW, _stream()), "quantize_u8")
