@@ -1,0 +1,118 @@
+"""GPU: the whole drop-in path (Finetunemodel.forward, RAFT.forward, update_cache) against
+the reference golden clips and the CPU oracle.  Tolerances are BASELINE.json's: flow EPE
+<= 0.01 px, frames >= 50 dB PSNR."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN, epe, psnr
+
+pytestmark = pytest.mark.gpu
+
+EPE_TOL = 0.01     # px, BASELINE.json north_star
+PSNR_TOL = 50.0    # dB
+
+
+@pytest.fixture(scope="module")
+def model_factory(weights, tmp_path_factory):
+    from zero_tig_b200 import synth
+    from zero_tig_b200.model.model import Finetunemodel
+    ck = tmp_path_factory.mktemp("w") / "synthetic-RLV.pt"
+    torch.save(weights, ck)
+
+    def make(of_scale):
+        m = Finetunemodel(synth.make_args(of_scale=of_scale, model_pretrain=str(ck))).cuda().eval()
+        m.raft.load_state_dict({k[5:]: v for k, v in weights.items() if k.startswith("raft.")})
+        return m
+    return make
+
+
+@pytest.mark.parametrize("tag", ["s1_128x160", "s3_390x400"])
+def test_finetune_clip_vs_reference_golden(tag, model_factory):
+    from zero_tig_b200 import synth, _lib
+    g = np.load(os.path.join(GOLDEN, f"infer_{tag}.npz"))
+    H, W, of_scale, n, stride = [int(v) for v in g["meta"]]
+    clip = synth.synthetic_clip(n, H, W, seed=3).cuda()
+    m = model_factory(of_scale)
+    before = _lib.launch_count()
+    for t in range(n):
+        m.is_new_seq = (t == 0)
+        H2, H3, s3 = m(clip[t:t + 1])
+        assert H2.shape == (1, 3, H, W) and H3.is_cuda
+        for name, v in (("H2", H2), ("H3", H3), ("s3", s3)):
+            ref = torch.from_numpy(g[f"{name}_{t}"])
+            p = psnr(v[0, :, ::stride, ::stride].cpu(), ref)
+            assert p >= PSNR_TOL, (name, t, p)
+    assert _lib.launch_count() - before > 100, "kernels did not launch through libzerotig"
+    eng = m.raft.engine()
+    # flow of the last pair: padded-size flow_up, strided like the fixture
+    fu = [v for k, v in eng.ws.bufs.items() if k[0] == "flow_up"][0]
+    e = epe(fu[0, :, ::stride, ::stride].cpu(), torch.from_numpy(g["flow_up_last"]))
+    assert e <= EPE_TOL, e
+    fl = eng.last["flow4"][:, :2].reshape(eng.last["h8"], eng.last["w8"], 2).permute(2, 0, 1).cpu()
+    assert epe(fl, torch.from_numpy(g["flow_low_last"])) <= EPE_TOL / 8
+
+
+def test_raft_forward_api_vs_oracle(weights, model_factory):
+    """RAFT.forward(image1, image2) public signature; trace intermediates vs the oracle."""
+    import zt_oracle as O
+    m = model_factory(1)
+    g = torch.Generator().manual_seed(4)
+    base = torch.rand(1, 3, 150, 170, generator=g)
+    im1 = (base * 255).round()
+    im2 = (torch.roll(base, (2, 3), (2, 3)) * 255).round()
+    tr = {}
+    fl_ref, fu_ref = O.raft_forward(im1, im2, weights, trace=tr)
+    fl, fu = m.raft(im1.cuda(), im2.cuda(), iters=12, test_mode=True)
+    assert fu.shape == fu_ref.shape == (1, 2, 152, 176)        # padded size is returned (Q3)
+    last = m.raft.engine().last
+    N = last["N"]
+    fm = last["fmap"].reshape(2, last["h8"], last["w8"], 256).permute(0, 3, 1, 2).cpu()
+    assert (fm[0] - tr["fmap1"][0]).abs().max().item() < 2e-4
+    assert (fm[1] - tr["fmap2"][0]).abs().max().item() < 2e-4
+    for i in range(4):
+        ref = tr["pyr"][i].reshape(N, -1)
+        assert (last["levels"][i].cpu() - ref).abs().max().item() < 5e-4
+    assert epe(fu.cpu(), fu_ref) <= EPE_TOL
+    assert epe(fl.cpu(), fl_ref) <= EPE_TOL / 8
+
+
+def test_update_cache_matches_oracle(weights, model_factory):
+    import zt_oracle as O
+    m = model_factory(3)
+    g = torch.Generator().manual_seed(8)
+    H, W = 384, 402
+    prev = torch.rand(1, 3, H, W, generator=g)
+    prev_s = torch.rand(1, 3, H, W, generator=g)
+    L2 = torch.clamp(torch.roll(prev, (3, 6), (2, 3)) * 0.2, 1e-4, 1)
+    ra, rb = O.update_cache(prev, prev_s, L2, weights, 3)
+    a, b = m.update_cache(prev.cuda(), prev_s.cuda(), L2.cuda())
+    assert psnr(a.cpu(), ra) >= PSNR_TOL and psnr(b.cpu(), rb) >= PSNR_TOL
+
+
+def test_new_sequence_resets_state(model_factory):
+    """is_new_seq=True must not read the previous state (model.py:319-321,330-332)."""
+    from zero_tig_b200 import synth
+    m = model_factory(3)
+    clip = synth.synthetic_clip(2, 384, 400, seed=5).cuda()
+    m.is_new_seq = True
+    a = [t.clone() for t in m(clip[0:1])]
+    m.is_new_seq = False
+    m(clip[1:2])
+    m.is_new_seq = True
+    b = m(clip[0:1])
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+
+
+def test_too_small_frame_is_refused(model_factory):
+    """Reference yields NaN when the coarsest pyramid level is 1 px; we raise."""
+    m = model_factory(3)
+    x = torch.rand(1, 3, 256, 256).cuda()
+    m.is_new_seq = True
+    m(x)
+    m.is_new_seq = False
+    with pytest.raises(RuntimeError, match="too small|NaN"):
+        m(x)
