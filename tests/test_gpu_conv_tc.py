@@ -1,0 +1,106 @@
+"""GPU: the tcgen05/TMEM implicit-GEMM convolution (csrc/conv_tc.cu) against an fp64 torch
+convolution of the same op.  split=3 (bf16 hi/lo, three products) must be fp32-grade
+(abs 1e-4 on O(1) outputs ~ 2^-16 relative per product); split=1 is plain bf16."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from test_gpu_ops import nchw, nhwc
+
+pytestmark = pytest.mark.gpu
+
+TC_CASES = [
+    # cin, cout, kh, kw, pad, H, W, B
+    (64, 64, 3, 3, (1, 1), 32, 16, 1),       # exact tiles
+    (64, 64, 3, 3, (1, 1), 45, 83, 1),       # ragged tiles
+    (32, 16, 1, 1, (0, 0), 16, 8, 1),        # one tile, one group, one tap
+    (48, 48, 3, 3, (1, 1), 70, 90, 1),       # cin not a multiple of 32 (denoise nets)
+    (384, 128, 1, 5, (0, 2), 23, 40, 1),     # GRU horizontal
+    (384, 128, 5, 1, (2, 0), 23, 40, 1),     # GRU vertical
+    (324, 256, 1, 1, (0, 0), 23, 40, 1),     # convc1 (cin%32 = 4)
+    (256, 126, 3, 3, (1, 1), 23, 40, 1),     # encoder.conv (cout not a multiple of 16)
+    (256, 2, 3, 3, (1, 1), 23, 40, 1),       # flow head
+    (2, 128, 7, 7, (3, 3), 23, 40, 1),       # convf1 (7x7 patch)
+    (256, 576, 1, 1, (0, 0), 23, 40, 1),     # mask head (5 N tiles)
+    (12, 64, 3, 3, (1, 1), 40, 56, 1),       # enhancer in_conv (cs 12)
+    (3, 48, 3, 3, (1, 1), 40, 56, 1),        # denoise_1 conv1 (cs 4)
+    (64, 3, 3, 3, (1, 1), 40, 56, 1),        # enhancer out_conv
+    (128, 128, 3, 3, (1, 1), 23, 40, 2),     # batch of two images (fnet)
+]
+
+
+@pytest.mark.parametrize("split", [3, 1])
+@pytest.mark.parametrize("case", TC_CASES)
+def test_conv_tc_matches_torch(case, split):
+    from zero_tig_b200 import ops
+    cin, cout, kh, kw, pad, H, W, B = case
+    g = torch.Generator().manual_seed(abs(hash(case)) % 1000)
+    x = torch.randn(B, cin, H, W, generator=g)
+    w = torch.randn(cout, cin, kh, kw, generator=g) / (cin * kh * kw) ** 0.5
+    b = torch.randn(cout, generator=g)
+    ref = F.leaky_relu(F.conv2d(x.double(), w.double(), b.double(), padding=pad), 0.2)
+    wt = ops.ConvW(w.cuda(), b.cuda())
+    Ho, Wo = ref.shape[-2:]
+    out_cs = (cout + 3) // 4 * 4
+    out = torch.full((B * Ho * Wo, out_cs), 777.0, device="cuda")
+    xin = nhwc(x)
+    ops.conv2d(wt, xin, xin.shape[1], wt.cin, B, H, W, out, out_cs, pad=pad, act="lrelu", tc=split)
+    torch.cuda.synchronize()
+    got = nchw(out, B, Ho, Wo, cout)
+    err = (got.double() - ref).abs().max().item()
+    assert err < (1e-4 if split == 3 else 5e-2), err
+    if out_cs > cout:   # padding channels are not written
+        assert (out[:, cout:] == 777.0).all()
+
+
+@pytest.mark.parametrize("bn", [16, 32, 64, 128, 256])
+def test_conv_tc_n_tiles(bn):
+    from zero_tig_b200 import ops
+    g = torch.Generator().manual_seed(bn)
+    x = torch.randn(1, 64, 20, 24, generator=g)
+    w = torch.randn(256, 64, 3, 3, generator=g) / 24.0
+    ref = F.conv2d(x.double(), w.double(), padding=1)
+    wt = ops.ConvW(w.cuda())
+    out = torch.zeros(20 * 24, 256, device="cuda")
+    xin = nhwc(x)
+    ops.conv2d(wt, xin, 64, 64, 1, 20, 24, out, 256, pad=(1, 1), tc=3, bn=bn)
+    err = (nchw(out, 1, 20, 24, 256).double() - ref).abs().max().item()
+    assert err < 1e-4, err
+
+
+def test_conv_tc_two_sources_and_gru_epilogues():
+    """virtual cat + fused GRU gates on the tensor-core path == SepConvGRU (update.py:45-60)."""
+    from zero_tig_b200 import ops
+    import zt_oracle as O
+    g = torch.Generator().manual_seed(5)
+    H, W = 23, 40
+    h = torch.tanh(torch.randn(1, 128, H, W, generator=g))
+    x = torch.randn(1, 256, H, W, generator=g)
+    wd = {}
+    for n in "zrq":
+        for s in "12":
+            wd[f"g.conv{n}{s}.weight"] = torch.randn(128, 384, *((1, 5) if s == "1" else (5, 1)), generator=g) * 0.03
+            wd[f"g.conv{n}{s}.bias"] = torch.randn(128, generator=g) * 0.1
+    ref = O.sep_conv_gru(h, x, wd, "g")
+    hx = nhwc(torch.cat([h, x], 1))
+    z = torch.empty(H * W, 128, device="cuda")
+    rh = torch.empty(H * W, 128, device="cuda")
+    for s, pad in (("1", (0, 2)), ("2", (2, 0))):
+        wzr = ops.ConvW(torch.cat([wd[f"g.convz{s}.weight"], wd[f"g.convr{s}.weight"]]).cuda(),
+                        torch.cat([wd[f"g.convz{s}.bias"], wd[f"g.convr{s}.bias"]]).cuda())
+        wq = ops.ConvW(wd[f"g.convq{s}.weight"].cuda(), wd[f"g.convq{s}.bias"].cuda())
+        ops.conv2d(wzr, hx, 384, 384, 1, H, W, rh, 128, pad=pad, epi="gru_zr", aux0=hx, aux0_cs=384, aux1=z,
+                   aux1_cs=128, tc=3, bn=64)
+        ops.conv2d(wq, rh, 128, 128, 1, H, W, hx, 384, in1=hx, in1_cs=384, c1=256, in1_off=128, pad=pad,
+                   epi="gru_q", aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128, tc=3, bn=64)
+    got = nchw(hx, 1, H, W, 128)
+    assert (got - ref).abs().max().item() < 1e-4
+
+
+def test_conv_tc_rejects_stride():
+    from zero_tig_b200 import ops
+    wt = ops.ConvW(torch.zeros(16, 32, 3, 3, device="cuda"))
+    x = torch.zeros(64, 32, device="cuda")
+    out = torch.zeros(16, 16, device="cuda")
+    with pytest.raises(RuntimeError, match="stride-1"):
+        ops.conv2d(wt, x, 32, 32, 1, 8, 8, out, 16, stride=2, pad=(1, 1), tc=3)

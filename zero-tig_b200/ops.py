@@ -30,7 +30,7 @@ def _p(t, offset_elems=0):
 
 class ConvW:
     """A conv layer's parameters in kernel layout: weight [kh][kw][cin_pad][w_cs], bias [cout]."""
-    __slots__ = ("w", "b", "kh", "kw", "cin", "cout", "w_cs")
+    __slots__ = ("w", "b", "kh", "kw", "cin", "cout", "w_cs", "w_raw", "_tc")
 
     def __init__(self, weight, bias=None, cin_pad=None, bn=None, eps=1e-5, out_slice=None):
         w = weight.detach().float()
@@ -51,11 +51,30 @@ class ConvW:
         wk[:, :, :cin, :cout] = w.permute(2, 3, 1, 0)
         self.w, self.b = wk.contiguous(), (None if b is None else b.contiguous())
         self.kh, self.kw, self.cin, self.cout, self.w_cs = kh, kw, cin_p, cout, w_cs
+        self.w_raw, self._tc = w, {}
+
+    def tc_pack(self, BN):
+        """bf16 hi/lo weights in the tcgen05 kernel's layout (csrc/conv_tc.cu):
+        [n_tile][32-channel group][tap][hi|lo][k-chunk 4][row BN][8] - one contiguous block per
+        (n_tile, group, tap) = one cp.async.bulk per weight-ring stage."""
+        t = self._tc.get(BN)
+        if t is None:
+            w = self.w_raw
+            cout, cin, kh, kw = w.shape
+            ng, nt = (self.cin + 31) // 32, (cout + BN - 1) // BN
+            wp = torch.zeros(nt * BN, ng * 32, kh, kw, device=w.device, dtype=torch.float32)
+            wp[:cout, :cin] = w
+            hi = wp.to(torch.bfloat16)
+            lo = (wp - hi.float()).to(torch.bfloat16)
+            x = torch.stack([hi, lo], 0).reshape(2, nt, BN, ng, 4, 8, kh * kw)
+            t = x.permute(1, 3, 6, 0, 4, 2, 5).contiguous()
+            self._tc[BN] = t
+        return t
 
 
 def conv2d(wt: ConvW, in0, in0_cs, c0, B, H, W, out, out_cs, *, in0_off=0, in1=None, in1_cs=0, c1=0,
            in1_off=0, out_off=0, stride=1, pad=(0, 0), act="none", scale=1.0, epi="plain",
-           aux0=None, aux0_cs=0, aux0_off=0, aux1=None, aux1_cs=0, aux1_off=0):
+           aux0=None, aux0_cs=0, aux0_off=0, aux1=None, aux1_cs=0, aux1_off=0, tc=0, bn=None):
     """out[:, out_off:out_off+cout] = epilogue(conv(cat[in0[:, in0_off:+c0], in1[:, in1_off:+c1]]))."""
     assert c0 + c1 == wt.cin, (c0, c1, wt.cin)
     sh = sw = stride
@@ -73,7 +92,13 @@ def conv2d(wt: ConvW, in0, in0_cs, c0, B, H, W, out, out_cs, *, in0_off=0, in1=N
     d.act, d.out_scale, d.epi = ACT[act], scale, EPI[epi]
     d.aux0, d.aux0_cs = _p(aux0, aux0_off), aux0_cs
     d.aux1, d.aux1_cs = _p(aux1, aux1_off), aux1_cs
-    check(lib().zt_conv2d_nhwc_f32(C.byref(d), _stream()), "conv2d")
+    if tc:
+        # tensor-core path: tc = 1 (bf16) or 3 (bf16 hi/lo split, 3 products ~ fp32-grade)
+        BN = bn or min((wt.cout + 15) // 16 * 16, 128)
+        d.weight = _p(wt.tc_pack(BN))
+        check(lib().zt_conv2d_tc_nhwc(C.byref(d), BN, tc, _stream()), "conv2d_tc")
+    else:
+        check(lib().zt_conv2d_nhwc_f32(C.byref(d), _stream()), "conv2d")
     return Ho, Wo
 
 
