@@ -74,7 +74,8 @@ def test_raft_forward_api_vs_oracle(weights, model_factory):
     assert (fm[1] - tr["fmap2"][0]).abs().max().item() < 2e-4
     for i in range(4):
         ref = tr["pyr"][i].reshape(N, -1)
-        assert (last["levels"][i].cpu() - ref).abs().max().item() < 5e-4
+        # correlation values are O(20): 1e-4 of the level's range (bf16 hi/lo split convs upstream)
+        assert (last["levels"][i].cpu() - ref).abs().max().item() < 1e-4 * ref.abs().max().item()
     assert epe(fu.cpu(), fu_ref) <= EPE_TOL
     assert epe(fl.cpu(), fl_ref) <= EPE_TOL / 8
 

@@ -38,8 +38,17 @@ def _param_version(module):
 # ----------------------------------------------------------------------------------------
 # RAFT
 # ----------------------------------------------------------------------------------------
+def _tc_mode(name, default):
+    """Tensor-core mode of a sub-network: 3 = bf16 hi/lo split (fp32-grade), 1 = plain bf16,
+    0 = fp32 CUDA-core kernel.  Overridable for experiments with ZT_TC_<NAME>."""
+    import os
+    return int(os.environ.get("ZT_TC_" + name, default))
+
+
 class RaftEngine:
     """RAFT.forward (model/RAFT/raft.py:77-130) on the kernels in csrc/."""
+
+    TC = _tc_mode("RAFT", 3)
 
     def __init__(self, raft):
         self.raft = raft
@@ -94,7 +103,7 @@ class RaftEngine:
 
     # ---- encoders (extractor.py:167-191) ----
     def _encoder(self, enc, x, B, H, W, is_bn):
-        w, ws = self.w, self.ws
+        w, ws, T = self.w, self.ws, self.TC
         stats = ws.get("in_stats", (B * 128 * 2,), torch.float64)
         h, wd = H // 2, W // 2
 
@@ -113,7 +122,7 @@ class RaftEngine:
                 ho, wo = h // s if s == 1 else (h + 2 - 3) // s + 1, wd // s if s == 1 else (wd + 2 - 3) // s + 1
                 t1 = buf(f"l{li}b{bi}.t1", ho, wo, cout)
                 ops.conv2d(w[p + ".conv1"], y, cin, cin, B, h, wd, t1, cout, stride=s, pad=(1, 1),
-                           act="relu" if is_bn else "none")
+                           act="relu" if is_bn else "none", tc=T if s == 1 else 0, bn=64)
                 if not is_bn:
                     ops.instnorm(t1, cout, t1, cout, stats, B, ho * wo, cout, relu_inner=True)
                 sc = y
@@ -125,10 +134,10 @@ class RaftEngine:
                 out = buf(f"l{li}b{bi}.out", ho, wo, cout)
                 if is_bn:
                     ops.conv2d(w[p + ".conv2"], t1, cout, cout, B, ho, wo, out, cout, pad=(1, 1), act="relu",
-                               epi="add_relu", aux0=sc, aux0_cs=cout)
+                               epi="add_relu", aux0=sc, aux0_cs=cout, tc=T, bn=64)
                 else:
                     t2 = buf(f"l{li}b{bi}.t2", ho, wo, cout)
-                    ops.conv2d(w[p + ".conv2"], t1, cout, cout, B, ho, wo, t2, cout, pad=(1, 1))
+                    ops.conv2d(w[p + ".conv2"], t1, cout, cout, B, ho, wo, t2, cout, pad=(1, 1), tc=T, bn=64)
                     ops.instnorm(t2, cout, out, cout, stats, B, ho * wo, cout, relu_inner=True, relu_outer=True,
                                  res=sc, res_cs=cout)
                 y, cin, h, wd = out, cout, ho, wo
@@ -140,7 +149,7 @@ class RaftEngine:
         Returns flow_up NCHW [1,2,hp,wp] (a workspace tensor, valid until the next call)."""
         _dev_check(x2)
         self._prepare(x2.device)
-        w, ws = self.w, self.ws
+        w, ws, T = self.w, self.ws, self.TC
         assert hp % 8 == 0 and wp % 8 == 0
         h8, w8 = hp // 8, wp // 8
         N = h8 * w8
@@ -148,7 +157,7 @@ class RaftEngine:
         f, fh, fw = self._encoder("fnet", x2, 2, hp, wp, False)
         assert (fh, fw) == (h8, w8)
         fmap = ws.get("fmap", (2 * N, 256))
-        ops.conv2d(w["fnet.conv2"], f, 128, 128, 2, h8, w8, fmap, 256)
+        ops.conv2d(w["fnet.conv2"], f, 128, 128, 2, h8, w8, fmap, 256, tc=T, bn=64)
         # all-pairs correlation volume + pyramid (corr.py:13-27,52-60)
         N4 = (N + 3) // 4 * 4
         f2t = ws.get("f2t", (256, N4))
@@ -169,8 +178,8 @@ class RaftEngine:
         # context network
         c, ch, cwid = self._encoder("cnet", x2, 1, hp, wp, True)
         hx = ws.get("hx", (N, 384))
-        ops.conv2d(w["cnet.conv2.net"], c, 128, 128, 1, h8, w8, hx, 384, act="tanh")
-        ops.conv2d(w["cnet.conv2.inp"], c, 128, 128, 1, h8, w8, hx, 384, out_off=128, act="relu")
+        ops.conv2d(w["cnet.conv2.net"], c, 128, 128, 1, h8, w8, hx, 384, act="tanh", tc=T, bn=64)
+        ops.conv2d(w["cnet.conv2.inp"], c, 128, 128, 1, h8, w8, hx, 384, out_off=128, act="relu", tc=T, bn=64)
         # iteration state
         grid = ws.bufs.get(("grid", h8, w8))
         if grid is None:
@@ -192,24 +201,24 @@ class RaftEngine:
         ops.flow_update(coords1, None, 0, flow4, 4, hx, 384, 382, h8, w8)
         for it in range(iters):
             ops.corr_lookup(lv, hs, wsz, coords1, corr, 324, N)
-            ops.conv2d(w["enc.convc1"], corr, 324, 324, 1, h8, w8, c1, 256, act="relu")
-            ops.conv2d(w["enc.convc2"], c1, 256, 256, 1, h8, w8, c2f, 256, pad=(1, 1), act="relu")
-            ops.conv2d(w["enc.convf1"], flow4, 4, 4, 1, h8, w8, f1, 128, pad=(3, 3), act="relu")
-            ops.conv2d(w["enc.convf2"], f1, 128, 128, 1, h8, w8, c2f, 256, out_off=192, pad=(1, 1), act="relu")
-            ops.conv2d(w["enc.conv"], c2f, 256, 256, 1, h8, w8, hx, 384, out_off=256, pad=(1, 1), act="relu")
+            ops.conv2d(w["enc.convc1"], corr, 324, 324, 1, h8, w8, c1, 256, act="relu", tc=T, bn=64)
+            ops.conv2d(w["enc.convc2"], c1, 256, 256, 1, h8, w8, c2f, 256, pad=(1, 1), act="relu", tc=T, bn=64)
+            ops.conv2d(w["enc.convf1"], flow4, 4, 4, 1, h8, w8, f1, 128, pad=(3, 3), act="relu", tc=T, bn=64)
+            ops.conv2d(w["enc.convf2"], f1, 128, 128, 1, h8, w8, c2f, 256, out_off=192, pad=(1, 1), act="relu", tc=T, bn=32)
+            ops.conv2d(w["enc.conv"], c2f, 256, 256, 1, h8, w8, hx, 384, out_off=256, pad=(1, 1), act="relu", tc=T, bn=64)
             for s, pad in (("1", (0, 2)), ("2", (2, 0))):
                 ops.conv2d(w["gru.zr" + s], hx, 384, 384, 1, h8, w8, rh, 128, pad=pad, epi="gru_zr",
-                           aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128)
+                           aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128, tc=T, bn=64)
                 ops.conv2d(w["gru.q" + s], rh, 128, 128, 1, h8, w8, hx, 384, in1=hx, in1_cs=384, c1=256,
-                           in1_off=128, pad=pad, epi="gru_q", aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128)
-            ops.conv2d(w["fh1"], hx, 384, 128, 1, h8, w8, fhid, 256, pad=(1, 1), act="relu")
-            ops.conv2d(w["fh2"], fhid, 256, 256, 1, h8, w8, delta, 4, pad=(1, 1))
+                           in1_off=128, pad=pad, epi="gru_q", aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128, tc=T, bn=32)
+            ops.conv2d(w["fh1"], hx, 384, 128, 1, h8, w8, fhid, 256, pad=(1, 1), act="relu", tc=T, bn=64)
+            ops.conv2d(w["fh2"], fhid, 256, 256, 1, h8, w8, delta, 4, pad=(1, 1), tc=T)
             ops.flow_update(coords1, delta, 4, flow4, 4, hx, 384, 382, h8, w8)
         # convex upsampling mask only for the returned (last) prediction (raft.py:122-130, Q15)
         mh = ws.get("maskh", (N, 256))
         mask = ws.get("mask", (N, 576))
-        ops.conv2d(w["mask0"], hx, 384, 128, 1, h8, w8, mh, 256, pad=(1, 1), act="relu")
-        ops.conv2d(w["mask2"], mh, 256, 256, 1, h8, w8, mask, 576, scale=0.25)
+        ops.conv2d(w["mask0"], hx, 384, 128, 1, h8, w8, mh, 256, pad=(1, 1), act="relu", tc=T, bn=64)
+        ops.conv2d(w["mask2"], mh, 256, 256, 1, h8, w8, mask, 576, scale=0.25, tc=T, bn=64)
         flow_up = ws.get("flow_up", (1, 2, hp, wp))
         ops.convex_upsample(flow4, 4, mask, 576, flow_up, h8, w8)
         self.last = dict(fmap=fmap, levels=lv, hs=hs, ws=wsz, flow4=flow4, hx=hx, corr=corr, N=N, h8=h8, w8=w8)
@@ -242,6 +251,9 @@ class FrameEngine:
     """Finetunemodel.forward / update_cache (model/model.py:312-384) on the kernels."""
 
     EPS = 1e-4
+    TC_D1 = _tc_mode("D1", 3)     # denoise_1 feeds the uint8 equalisation cliff: keep fp32-grade
+    TC_ENH = _tc_mode("ENH", 3)
+    TC_D2 = _tc_mode("D2", 3)
 
     def __init__(self, model):
         self.model = model
@@ -278,9 +290,9 @@ class FrameEngine:
         a2 = ws.get("a48b", (HW, 48))
         d = ws.get("d4", (HW, 4))
         ops.pack_nhwc([x], 3, self.EPS, xp, 4, HW)
-        ops.conv2d(w["d1.c1"], xp, 4, 4, 1, H, W, a1, 48, pad=(1, 1), act="lrelu")
-        ops.conv2d(w["d1.c2"], a1, 48, 48, 1, H, W, a2, 48, pad=(1, 1), act="lrelu")
-        ops.conv2d(w["d1.c3"], a2, 48, 48, 1, H, W, d, 4)
+        ops.conv2d(w["d1.c1"], xp, 4, 4, 1, H, W, a1, 48, pad=(1, 1), act="lrelu", tc=self.TC_D1)
+        ops.conv2d(w["d1.c2"], a1, 48, 48, 1, H, W, a2, 48, pad=(1, 1), act="lrelu", tc=self.TC_D1)
+        ops.conv2d(w["d1.c3"], a2, 48, 48, 1, H, W, d, 4, tc=self.TC_D1)
         L2 = torch.empty_like(x)
         ops.retinex_l2(x, d, 4, L2, HW, self.EPS)
         return L2
@@ -293,13 +305,13 @@ class FrameEngine:
         fb = ws.get("f64b", (HW, 64))
         s4 = ws.get("s4", (HW, 4))
         ops.pack_nhwc([H3_wp, s3_wp, L2], 3, 0.0, ep, 12, HW)
-        ops.conv2d(w["e.in"], ep, 12, 12, 1, H, W, fa, 64, pad=(1, 1), act="relu")
+        ops.conv2d(w["e.in"], ep, 12, 12, 1, H, W, fa, 64, pad=(1, 1), act="relu", tc=self.TC_ENH)
         cur, nxt = fa, fb
         for _ in range(3):  # one shared conv+BN applied three times (model.py:60-67, Q5)
             ops.conv2d(w["e.blk"], cur, 64, 64, 1, H, W, nxt, 64, pad=(1, 1), act="relu", epi="add",
-                       aux0=cur, aux0_cs=64)
+                       aux0=cur, aux0_cs=64, tc=self.TC_ENH)
             cur, nxt = nxt, cur
-        ops.conv2d(w["e.out"], cur, 64, 64, 1, H, W, s4, 4, pad=(1, 1), act="sigmoid")
+        ops.conv2d(w["e.out"], cur, 64, 64, 1, H, W, s4, 4, pad=(1, 1), act="sigmoid", tc=self.TC_ENH)
         s2 = torch.empty_like(x)
         H2 = torch.empty_like(x)
         ops.retinex_h2(x, s4, 4, s2, H2, HW, self.EPS)
@@ -313,9 +325,9 @@ class FrameEngine:
         a2 = ws.get("a48b", (HW, 48))
         d = ws.get("d8", (HW, 8))
         ops.pack_nhwc([H3_wp, s3_wp, H2, s2], 3, 0.0, dp, 12, HW)
-        ops.conv2d(w["d2.c1"], dp, 12, 12, 1, H, W, a1, 48, pad=(1, 1), act="lrelu")
-        ops.conv2d(w["d2.c2"], a1, 48, 48, 1, H, W, a2, 48, pad=(1, 1), act="lrelu")
-        ops.conv2d(w["d2.c3"], a2, 48, 48, 1, H, W, d, 8)
+        ops.conv2d(w["d2.c1"], dp, 12, 12, 1, H, W, a1, 48, pad=(1, 1), act="lrelu", tc=self.TC_D2)
+        ops.conv2d(w["d2.c2"], a1, 48, 48, 1, H, W, a2, 48, pad=(1, 1), act="lrelu", tc=self.TC_D2)
+        ops.conv2d(w["d2.c3"], a2, 48, 48, 1, H, W, d, 8, tc=self.TC_D2)
         H3 = torch.empty_like(H2)
         s3 = torch.empty_like(H2)
         ops.retinex_h5(H2, s2, d, 8, H3, s3, HW, self.EPS)
