@@ -76,6 +76,10 @@ int zt_conv2d_nhwc_f32(const ZtConv* d, void* stream);
  * in [16,256].  Same call sites as zt_conv2d_nhwc_f32. */
 int zt_conv2d_tc_nhwc(const ZtConv* d, int BN, int split, void* stream);
 
+/* debug only: per-role timeline of CTA (0,0) of the next zt_conv2d_tc_nhwc launches; buf is a
+ * device int64 array [1 + 2*cap] (zeroed by the caller), NULL disables. */
+int zt_debug_set_tc_trace(void* buf, int cap);
+
 /* ---- InstanceNorm2d (affine=False, eps) on NHWC fp32; extractor.py:27-31,129 -------------
  * stats: per (image, channel) sums in fp64 scratch `stats` [B][C][2] (zeroed inside).
  * apply: y = norm(x); if relu_inner y=relu(y); if res: y = res + y; if relu_outer y=relu(y) */

@@ -26,6 +26,10 @@ TC_CASES = [
     (3, 48, 3, 3, (1, 1), 40, 56, 1),        # denoise_1 conv1 (cs 4)
     (64, 3, 3, 3, (1, 1), 40, 56, 1),        # enhancer out_conv
     (128, 128, 3, 3, (1, 1), 23, 40, 2),     # batch of two images (fnet)
+    (64, 64, 3, 3, (1, 1), 203, 211, 1),     # 338 tiles > 148 CTAs: persistent loop, resident weights
+    (48, 48, 3, 3, (1, 1), 150, 330, 2),     # persistent + batch + cin%32 != 0
+    (256, 256, 3, 3, (1, 1), 100, 100, 1),   # persistent with the streamed weight ring (wraps)
+    (12, 6, 1, 1, (0, 0), 300, 200, 1),      # tiny K, persistent
 ]
 
 

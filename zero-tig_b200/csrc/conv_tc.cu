@@ -26,8 +26,15 @@ namespace zt {
 constexpr int TC_TW = 8;          // tile width in pixels (= one 8-row core-matrix group)
 constexpr int TC_TH = 16;         // tile height -> 128 GEMM rows
 constexpr int TC_CG = 32;         // channels per A stage (4 chunks of 8)
-constexpr int TC_NA = 2;          // A ring depth
-constexpr int TC_THREADS = 192;   // warps 0-3 producer+epilogue, warp 4 MMA, warp 5 weight loader
+// warps 0-7 epilogue (warp%4 = TMEM lane quadrant, warp/4 = odd/even 16-column groups),
+// 8 MMA issuer, 9 weight loader, 10-13 producer group 0, 14-17 producer group 1
+// (the producer groups alternate A stages)
+constexpr int TC_THREADS = 576;
+constexpr int TC_PB = 12;         // patch pixels (float4 loads) in flight per producer thread
+constexpr int TC_W_MMA = 8, TC_W_LOAD = 9, TC_W_PROD = 10;
+constexpr int TC_BAR_BYTES = 1024;
+constexpr int TC_EPI_LD = 36;                               // staging row pitch in floats (32 + 4 pad)
+constexpr int TC_EPI_BYTES = 8 * 32 * TC_EPI_LD * 4;        // 8 epilogue warps x 32 rows
 
 struct TcGeom {
   int BN;            // N tile (multiple of 16, <= 256)
@@ -36,9 +43,27 @@ struct TcGeom {
   int PW, P;         // patch width, patch pixels
   int lboA;          // bytes between k-chunks of the A patch
   int tiles_x, tiles_y;
-  int NB;            // weight ring depth
-  int tmem_cols;     // power of two >= 32
+  int NA;            // A (patch) ring depth
+  int NB;            // weight ring depth (resident: number of weight stages = ngroups*ntaps)
+  int resident;      // 1: all weights of this N tile stay in shared memory for every pixel tile
+  int tmem_cols;     // power of two >= 32, holds two accumulators of BN columns
+  int S;             // pixel tiles over all images = tiles_x*tiles_y*B
+  long long* trace;  // debug: per-role timestamps of CTA (0,0) (zt_debug_set_tc_trace), else NULL
+  int trace_cap;
 };
+
+// debug timeline: record (role, tile/stage index, event, globaltimer ns) for CTA (0,0)
+__device__ __forceinline__ void tc_trace(const TcGeom& g, int role, int idx, int ev) {
+  if (g.trace && blockIdx.x == 0 && blockIdx.y == 0) {
+    long long tns;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tns));
+    const int slot = (int)atomicAdd(reinterpret_cast<unsigned long long*>(g.trace), 1ull);
+    if (slot < g.trace_cap) {
+      g.trace[1 + 2 * slot] = ((long long)role << 48) | ((long long)ev << 32) | (unsigned)idx;
+      g.trace[2 + 2 * slot] = tns;
+    }
+  }
+}
 
 // ---------------------------------------------------------------- PTX helpers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -107,85 +132,110 @@ __device__ __forceinline__ void split4(const float4 v, uint2& hi, uint2& lo) {
   lo.y = (uint32_t)__bfloat16_as_ushort(l2) | ((uint32_t)__bfloat16_as_ushort(l3) << 16);
 }
 
-// ---------------------------------------------------------------- epilogue (4 consecutive channels)
-__device__ __forceinline__ void tc_epilogue4(const ZtConv& d, int64_t m, int nb, float x0, float x1, float x2,
-                                             float x3) {
+// ---------------------------------------------------------------- epilogue
+__device__ __forceinline__ float4 ld4_or_scalar(const float* p, int nvalid) {
+  if (nvalid >= 4 && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) return *reinterpret_cast<const float4*>(p);
+  float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (nvalid > 0) r.x = p[0];
+  if (nvalid > 1) r.y = p[1];
+  if (nvalid > 2) r.z = p[2];
+  if (nvalid > 3) r.w = p[3];
+  return r;
+}
+
+template <int ACT>
+__device__ __forceinline__ float act_t(float v, int act_rt) {
+  if constexpr (ACT == ZT_ACT_NONE) return v;
+  else if constexpr (ACT == ZT_ACT_RELU) return fmaxf(v, 0.f);
+  else if constexpr (ACT == ZT_ACT_LRELU02) return v > 0.f ? v : 0.2f * v;
+  else if constexpr (ACT == ZT_ACT_SIGMOID) return 1.f / (1.f + expf(-v));
+  else if constexpr (ACT == ZT_ACT_TANH) return tanhf(v);
+  else return apply_act(v, act_rt);
+}
+
+// EPI / ACT are compile-time for the combinations the hot path uses (the epilogue warps
+// bound the kernel otherwise); EPI_T = -1 is the generic run-time fallback.
+template <int EPI_T, int ACT_T>
+__device__ __forceinline__ void tc_epilogue4(const ZtConv& d, int64_t m, int nb, int nend, float x0, float x1,
+                                             float x2, float x3, const float4 bv, const float4 a0v,
+                                             const float4 a1v) {
+  const int epi = EPI_T >= 0 ? EPI_T : d.epi;
   float v[4] = {x0, x1, x2, x3};
+  const float a0[4] = {a0v.x, a0v.y, a0v.z, a0v.w}, a1[4] = {a1v.x, a1v.y, a1v.z, a1v.w};
   const int Ch = d.cout >> 1;
+  const int nvalid = min(4, nend - nb);   // nend: end of this CTA's channel range
+  if (nvalid <= 0) return;
+  const float b[4] = {bv.x, bv.y, bv.z, bv.w};
 #pragma unroll
   for (int e = 0; e < 4; ++e) {
-    const int n = nb + e;
-    if (n >= d.cout) { v[e] = 0.f; continue; }
-    float x = v[e];
-    if (d.bias) x += __ldg(d.bias + n);
-    switch (d.epi) {
-      case ZT_EPI_GRU_ZR:
-        x = 1.f / (1.f + expf(-x));
-        if (n >= Ch) x *= d.aux0[m * d.aux0_cs + (n - Ch)];
-        break;
-      case ZT_EPI_GRU_Q: {
-        const float z = d.aux1[m * d.aux1_cs + n];
-        const float h = d.aux0[m * d.aux0_cs + n];
-        x = (1.f - z) * h + z * tanhf(x);
-      } break;
-      case ZT_EPI_ADD_RELU:
-        x = fmaxf(d.aux0[m * d.aux0_cs + n] + apply_act(x, d.act) * d.out_scale, 0.f);
-        break;
-      case ZT_EPI_ADD:
-        x = d.aux0[m * d.aux0_cs + n] + apply_act(x, d.act) * d.out_scale;
-        break;
-      default:
-        x = apply_act(x, d.act) * d.out_scale;
+    float x = v[e] + b[e];
+    if (epi == ZT_EPI_GRU_ZR) {
+      x = 1.f / (1.f + expf(-x));
+      if (nb >= Ch) x *= a0[e];
+    } else if (epi == ZT_EPI_GRU_Q) {
+      x = (1.f - a1[e]) * a0[e] + a1[e] * tanhf(x);
+    } else if (epi == ZT_EPI_ADD_RELU) {
+      x = fmaxf(a0[e] + act_t<ACT_T>(x, d.act) * d.out_scale, 0.f);
+    } else if (epi == ZT_EPI_ADD) {
+      x = a0[e] + act_t<ACT_T>(x, d.act) * d.out_scale;
+    } else {
+      x = act_t<ACT_T>(x, d.act) * d.out_scale;
     }
     v[e] = x;
   }
   float* dst;
   int dn, dcs;
-  if (d.epi == ZT_EPI_GRU_ZR && nb < Ch) { dst = d.aux1; dn = nb; dcs = d.aux1_cs; }
-  else if (d.epi == ZT_EPI_GRU_ZR)       { dst = d.out; dn = nb - Ch; dcs = d.out_cs; }
-  else                                   { dst = d.out; dn = nb; dcs = d.out_cs; }
+  if (epi == ZT_EPI_GRU_ZR && nb < Ch) { dst = d.aux1; dn = nb; dcs = d.aux1_cs; }
+  else if (epi == ZT_EPI_GRU_ZR)       { dst = d.out; dn = nb - Ch; dcs = d.out_cs; }
+  else                                 { dst = d.out; dn = nb; dcs = d.out_cs; }
   float* p = dst + m * dcs + dn;
-  if (nb + 3 < d.cout && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
+  if (nvalid == 4 && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
     *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
   } else {
 #pragma unroll
     for (int e = 0; e < 4; ++e)
-      if (nb + e < d.cout) p[e] = v[e];
+      if (e < nvalid) p[e] = v[e];
   }
 }
 
 // ---------------------------------------------------------------- kernel
-template <int SPLIT>
-__global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const ZtConv d, const TcGeom g) {
+// Persistent, warp-specialised: each CTA (one per SM) walks pixel tiles t = blockIdx.x,
+// +gridDim.x, ... of N tile blockIdx.y.  Two producer groups alternate A stages so two patch
+// loads are in flight; accumulators are double-buffered in TMEM so the epilogue of tile i
+// overlaps the MMAs of tile i+1; small weight sets stay resident in shared memory.
+template <int SPLIT, int EPI_T, int ACT_T>
+__global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, const TcGeom g) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr int NPART = SPLIT == 3 ? 2 : 1;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 240);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TC_BAR_BYTES - 16);
   const uint32_t a_part = 4u * g.lboA, a_stage = a_part * NPART;
   const uint32_t b_part = 4u * g.BN * 16u, b_stage = b_part * NPART;
-  uint8_t* smA = smem + 256;
-  uint8_t* smB = smA + TC_NA * a_stage;
-  const uint32_t bar0 = smem_u32(bars);
-  auto fullA = [&](int s) { return bar0 + 8u * s; };
-  auto emptyA = [&](int s) { return bar0 + 8u * (TC_NA + s); };
-  auto fullB = [&](int s) { return bar0 + 8u * (2 * TC_NA + s); };
-  auto emptyB = [&](int s) { return bar0 + 8u * (2 * TC_NA + g.NB + s); };
-  const uint32_t accFull = bar0 + 8u * (2 * TC_NA + 2 * g.NB);
+  uint8_t* smA = smem + TC_BAR_BYTES + TC_EPI_BYTES;
+  uint8_t* smB = smA + g.NA * a_stage;
+  const uint32_t bar0 = smem_u32(smem);
+  const int NA = g.NA, NB = g.NB;
+  const int NBb = g.resident ? 1 : NB;      // number of weight barriers in use
+  auto fullA = [&](uint32_t s) { return bar0 + 8u * s; };
+  auto emptyA = [&](uint32_t s) { return bar0 + 8u * (NA + s); };
+  auto fullB = [&](uint32_t s) { return bar0 + 8u * (2 * NA + s); };
+  auto emptyB = [&](uint32_t s) { return bar0 + 8u * (2 * NA + NBb + s); };
+  auto accFull = [&](uint32_t s) { return bar0 + 8u * (2 * NA + 2 * NBb + s); };
+  auto accEmpty = [&](uint32_t s) { return bar0 + 8u * (2 * NA + 2 * NBb + 2 + s); };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tyi = blockIdx.x / g.tiles_x, txi = blockIdx.x - tyi * g.tiles_x;
-  const int oy0 = tyi * TC_TH, ox0 = txi * TC_TW;
   const int n0 = blockIdx.y * g.BN;
-  const int bimg = blockIdx.z;
   const int cin = d.c0 + d.c1;
+  const int tiles_per_img = g.tiles_x * g.tiles_y;
+  const int S = g.S, ngroups = g.ngroups, ntaps = g.ntaps;
+  const uint32_t nstage = (uint32_t)ngroups * ntaps;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < TC_NA; ++s) { mbar_init(fullA(s), 128); mbar_init(emptyA(s), 1); }
-    for (int s = 0; s < g.NB; ++s) { mbar_init(fullB(s), 1); mbar_init(emptyB(s), 1); }
-    mbar_init(accFull, 1);
+    for (int s = 0; s < NA; ++s) { mbar_init(fullA(s), 128); mbar_init(emptyA(s), 1); }
+    for (int s = 0; s < NBb; ++s) { mbar_init(fullB(s), 1); mbar_init(emptyB(s), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(accFull(s), 1); mbar_init(accEmpty(s), 256); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 4) {
+  if (warp == TC_W_MMA) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
                  ::"r"(smem_u32(tmem_slot)), "r"((uint32_t)g.tmem_cols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -195,130 +245,287 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const ZtConv d, con
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp < 4) {
+  if (warp < 8) {
+    // ===================== epilogue: TMEM -> registers -> smem transpose -> global ===========
+    // tcgen05.ld hands thread i row i of the tile; a direct store would touch 32 lines per
+    // instruction.  Each warp transposes its 32 rows x 32 columns through a padded staging
+    // tile so that 8 lanes cover 128 contiguous bytes of one pixel (4 full lines per
+    // instruction) for the residual/gate loads and the output stores alike.
+    const int quad = warp & 3, half = warp >> 2;
+    float* stage = reinterpret_cast<float*>(smem + TC_BAR_BYTES) + warp * 32 * TC_EPI_LD;
+    const int piece = lane & 7, rsub = lane >> 3;
+    const int nend = min(d.cout, n0 + g.BN);        // this CTA owns output channels [n0, nend)
+    const int nchunk = (nend - n0 + 31) >> 5;
+    const int epi = EPI_T >= 0 ? EPI_T : d.epi;
+    const int Ch = d.cout >> 1;
+    uint32_t lt = 0;
+    for (int t = blockIdx.x; t < S; t += gridDim.x, ++lt) {
+      const int bimg = t / tiles_per_img, tr = t - bimg * tiles_per_img;
+      const int tyi = tr / g.tiles_x, txi = tr - tyi * g.tiles_x;
+      const int oyb = tyi * TC_TH + quad * 4, oxb = txi * TC_TW + rsub;
+      const int64_t mb = ((int64_t)bimg * d.Ho + oyb) * d.Wo + oxb;
+      const uint32_t buf = lt & 1;
+      bool waited = false;
+      for (int ch = half; ch < nchunk; ch += 2) {
+        const int nb = n0 + ch * 32 + piece * 4;          // this thread's 4 output channels
+        const int nvalid = nend - nb;
+        // residual / gate operands do not depend on the MMAs: fetch them before waiting
+        float4 a0[8], a1[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          a0[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+          a1[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+          const bool okk = (oyb + (k >> 1) < d.Ho) && (oxb + 4 * (k & 1) < d.Wo) && nvalid > 0;
+          if (okk && epi != ZT_EPI_PLAIN) {
+            const int64_t m = mb + (int64_t)(k >> 1) * d.Wo + 4 * (k & 1);
+            if (epi == ZT_EPI_GRU_ZR) {
+              if (nb >= Ch) a0[k] = ld4_or_scalar(d.aux0 + m * d.aux0_cs + (nb - Ch), nvalid);
+            } else {
+              a0[k] = ld4_or_scalar(d.aux0 + m * d.aux0_cs + nb, nvalid);
+              if (epi == ZT_EPI_GRU_Q) a1[k] = ld4_or_scalar(d.aux1 + m * d.aux1_cs + nb, nvalid);
+            }
+          }
+        }
+        float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (d.bias && nvalid > 0) bv = ld4_or_scalar(d.bias + nb, nvalid);
+        if (!waited) {
+          if (lane == 0) tc_trace(g, warp, lt, 0);
+          mbar_wait(accFull(buf), (lt >> 1) & 1);
+          tc_fence_after();
+          waited = true;
+          if (lane == 0) tc_trace(g, warp, lt, 1);
+        }
+        const uint32_t taddr = tmem_base + buf * (uint32_t)g.BN + ((uint32_t)(quad * 32) << 16) + (uint32_t)(ch * 32);
+        uint32_t v[16];
+        tmem_ld16(taddr, v);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          *reinterpret_cast<uint4*>(stage + lane * TC_EPI_LD + 4 * i) = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        if (ch * 32 + 16 < g.BN) {      // the second half of the chunk exists in TMEM (BN % 32 may be 16)
+          tmem_ld16(taddr + 16, v);
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            *reinterpret_cast<uint4*>(stage + lane * TC_EPI_LD + 16 + 4 * i) = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const bool okk = (oyb + (k >> 1) < d.Ho) && (oxb + 4 * (k & 1) < d.Wo) && nvalid > 0;
+          if (okk) {
+            const float4 x = *reinterpret_cast<const float4*>(stage + (4 * k + rsub) * TC_EPI_LD + piece * 4);
+            const int64_t m = mb + (int64_t)(k >> 1) * d.Wo + 4 * (k & 1);
+            tc_epilogue4<EPI_T, ACT_T>(d, m, nb, nend, x.x, x.y, x.z, x.w, bv, a0[k], a1[k]);
+          }
+        }
+        __syncwarp();
+      }
+      if (!waited) { mbar_wait(accFull(buf), (lt >> 1) & 1); tc_fence_after(); }
+      tc_fence_before();
+      mbar_arrive(accEmpty(buf));
+      if (lane == 0) tc_trace(g, warp, lt, 2);
+    }
+  } else if (warp == TC_W_MMA) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      const uint32_t BN = g.BN, PW = g.PW, kh = d.kh, kw = d.kw;
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((BN >> 3) << 17) | (8u << 24);
+      const uint32_t lboA = g.lboA, lboB = BN * 16u;
+      // descriptor templates: only the 14-bit start-address field (16 B units) changes per MMA
+      const uint64_t descA0 = make_desc(0, lboA, PW * 16u), descB0 = make_desc(0, lboB, 128u);
+      const uint32_t ksA = (2u * lboA) >> 4, ksB = (2u * lboB) >> 4;
+      const uint32_t apart16 = a_part >> 4, bpart16 = b_part >> 4;
+      const uint32_t smA16 = smem_u32(smA) >> 4, smB16 = smem_u32(smB) >> 4;
+      const uint32_t a_stage16 = a_stage >> 4, b_stage16 = b_stage >> 4;
+      const bool resident = g.resident != 0;
+      uint32_t ia = 0, ib = 0, lt = 0;
+      uint32_t sa = 0, pa = 0;          // A ring slot / parity
+      uint32_t sbr = 0, pb = 0;         // B ring slot / parity (streamed mode)
+      if (resident) { mbar_wait(fullB(0), 0); tc_fence_after(); }
+      for (int t = blockIdx.x; t < S; t += gridDim.x, ++lt) {
+        const uint32_t buf = lt & 1;
+        tc_trace(g, TC_W_MMA, lt, 3);
+        mbar_wait(accEmpty(buf), ((lt >> 1) & 1) ^ 1);
+        tc_fence_after();
+        tc_trace(g, TC_W_MMA, lt, 4);
+        const uint32_t tmem_d = tmem_base + buf * BN;
+        uint32_t acc = 0;
+        int crem = cin;
+        uint32_t bres16 = smB16;        // resident mode: walks the weight stages in order
+        for (int gi = 0; gi < ngroups; ++gi, crem -= TC_CG) {
+          tc_trace(g, TC_W_MMA, lt * ngroups + gi, 0);
+          mbar_wait(fullA(sa), pa);
+          tc_fence_after();
+          tc_trace(g, TC_W_MMA, lt * ngroups + gi, 1);
+          const bool two = crem > 16;
+          const uint32_t a16 = smA16 + sa * a_stage16;
+          uint32_t row16 = a16;
+          for (uint32_t ky = 0; ky < kh; ++ky, row16 += PW) {
+            for (uint32_t kx = 0; kx < kw; ++kx) {
+              uint32_t b16;
+              if (resident) {
+                b16 = bres16;
+                bres16 += b_stage16;
+              } else {
+                mbar_wait(fullB(sbr), pb);
+                tc_fence_after();
+                b16 = smB16 + sbr * b_stage16;
+              }
+              const uint64_t dah = descA0 + (row16 + kx), dbh = descB0 + b16;
+              tc_mma_bf16(tmem_d, dah, dbh, idesc, acc);
+              acc = 1;
+              if (SPLIT == 3) {
+                tc_mma_bf16(tmem_d, dah + apart16, dbh, idesc, 1);
+                tc_mma_bf16(tmem_d, dah, dbh + bpart16, idesc, 1);
+              }
+              if (two) {
+                tc_mma_bf16(tmem_d, dah + ksA, dbh + ksB, idesc, 1);
+                if (SPLIT == 3) {
+                  tc_mma_bf16(tmem_d, dah + ksA + apart16, dbh + ksB, idesc, 1);
+                  tc_mma_bf16(tmem_d, dah + ksA, dbh + ksB + bpart16, idesc, 1);
+                }
+              }
+              if (!resident) {
+                tc_commit(emptyB(sbr));
+                if (++sbr == (uint32_t)NB) { sbr = 0; pb ^= 1; }
+              }
+            }
+          }
+          tc_commit(emptyA(sa));
+          tc_trace(g, TC_W_MMA, lt * ngroups + gi, 2);
+          if (++sa == (uint32_t)NA) { sa = 0; pa ^= 1; }
+        }
+        tc_commit(accFull(buf));
+      }
+      (void)ia; (void)ib;
+    }
+    __syncwarp();
+  } else if (warp == TC_W_LOAD) {
+    // ===================== weight loader (one thread, bulk async copies) =====================
+    if (lane == 0) {
+      const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(d.weight) + (size_t)blockIdx.y * nstage * (2u * b_part);
+      if (g.resident) {
+        if ((int)blockIdx.x < S) {
+          mbar_arrive_expect_tx(fullB(0), nstage * b_stage);
+          for (uint32_t it = 0; it < nstage; ++it)
+            bulk_g2s(smem_u32(smB + it * b_stage), wsrc + (size_t)it * (2u * b_part), b_stage, fullB(0));
+        }
+      } else {
+        uint32_t sb = 0, pb = 1;
+        for (int t = blockIdx.x; t < S; t += gridDim.x) {
+          for (uint32_t it = 0; it < nstage; ++it) {
+            mbar_wait(emptyB(sb), pb);
+            mbar_arrive_expect_tx(fullB(sb), b_stage);
+            bulk_g2s(smem_u32(smB + sb * b_stage), wsrc + (size_t)it * (2u * b_part), b_stage, fullB(sb));
+            if (++sb == (uint32_t)NB) { sb = 0; pb ^= 1; }
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else {
     // ===================== producers: fp32 patch -> bf16 hi/lo canonical smem =====================
-    const int tid = threadIdx.x;
+    // Group pg owns A stages ia = pg, pg+2, ...  The global loads of a stage are issued BEFORE
+    // waiting for its ring slot (they only need registers), so the HBM/L2 latency overlaps the
+    // wait for the MMAs that free the slot.
+    const int pg = (warp - TC_W_PROD) >> 2;                      // producer group 0 / 1
+    const int tid = threadIdx.x - TC_W_PROD * 32 - pg * 128;     // 0..127 within the group
     const int q = tid & 7, pl = tid >> 3;
+    const int P = g.P, PW = g.PW;
     const uint32_t soff = (uint32_t)(q >> 1) * g.lboA + (uint32_t)(q & 1) * 8u;
-    const int64_t img_pix = (int64_t)bimg * d.H * d.W;
-    for (int gi = 0; gi < g.ngroups; ++gi) {
-      const int s = gi & 1;
-      mbar_wait(emptyA(s), ((gi >> 1) & 1) ^ 1);
-      uint8_t* dst_hi = smA + s * a_stage;
+    const int py0 = pl / PW, px0 = pl - py0 * PW;
+    const int ntl = S > (int)blockIdx.x ? (S - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    const uint32_t nia = (uint32_t)ntl * ngroups;
+
+    // per-stage source description
+    const float* src = nullptr;
+    int cs = 0, iy0 = 0, ix0 = 0;
+    int64_t img_pix = 0;
+    bool cvalid = false;
+    auto setup = [&](uint32_t ia) {
+      const int lt = ia / ngroups, gi = ia - lt * ngroups;
+      const int t = blockIdx.x + lt * gridDim.x;
+      const int bimg = t / tiles_per_img, tr = t - bimg * tiles_per_img;
+      const int tyi = tr / g.tiles_x, txi = tr - tyi * g.tiles_x;
+      iy0 = tyi * TC_TH - d.ph;
+      ix0 = txi * TC_TW - d.pw;
+      img_pix = (int64_t)bimg * d.H * d.W;
       const int c = gi * TC_CG + q * 4;
-      const bool cvalid = c < cin;
-      const float* src = d.in0;
-      int cs = d.in0_cs;
+      cvalid = c < cin;
+      src = d.in0; cs = d.in0_cs;
       if (cvalid) {
         if (c < d.c0) { src = d.in0 + c; }
         else { src = d.in1 + (c - d.c0); cs = d.in1_cs; }
       }
-      int py = pl / g.PW, px = pl - py * g.PW;
-      for (int p0 = pl; p0 < g.P; p0 += 64) {
-        float4 v[4];
+    };
+    auto load_batch = [&](float4 (&v)[TC_PB], int p0, int& py, int& px) {
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int p = p0 + 16 * u;
-          const int iy = oy0 - d.ph + py, ix = ox0 - d.pw + px;
-          v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (cvalid && p < g.P && iy >= 0 && iy < d.H && ix >= 0 && ix < d.W)
-            v[u] = __ldg(reinterpret_cast<const float4*>(src + (img_pix + (int64_t)iy * d.W + ix) * cs));
-          px += 16;
-          while (px >= g.PW) { px -= g.PW; ++py; }
-        }
+      for (int u = 0; u < TC_PB; ++u) {
+        const int p = p0 + 16 * u;
+        const int iy = iy0 + py, ix = ix0 + px;
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (cvalid && p < P && iy >= 0 && iy < d.H && ix >= 0 && ix < d.W)
+          v[u] = __ldg(reinterpret_cast<const float4*>(src + (img_pix + (int64_t)iy * d.W + ix) * cs));
+        px += 16;
+        while (px >= PW) { px -= PW; ++py; }
+      }
+    };
+    auto store_batch = [&](const float4 (&v)[TC_PB], int p0, uint8_t* dst_hi) {
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int p = p0 + 16 * u;
-          if (p < g.P) {
-            uint2 hi, lo;
-            split4(v[u], hi, lo);
-            *reinterpret_cast<uint2*>(dst_hi + soff + (uint32_t)p * 16u) = hi;
-            if (SPLIT == 3) *reinterpret_cast<uint2*>(dst_hi + a_part + soff + (uint32_t)p * 16u) = lo;
-          }
+      for (int u = 0; u < TC_PB; ++u) {
+        const int p = p0 + 16 * u;
+        if (p < P) {
+          uint2 hi, lo;
+          split4(v[u], hi, lo);
+          *reinterpret_cast<uint2*>(dst_hi + soff + (uint32_t)p * 16u) = hi;
+          if (SPLIT == 3) *reinterpret_cast<uint2*>(dst_hi + a_part + soff + (uint32_t)p * 16u) = lo;
         }
+      }
+    };
+
+    float4 v[TC_PB];
+    int py = py0, px = px0;
+    uint32_t ia = pg;
+    if (ia < nia) { setup(ia); load_batch(v, pl, py, px); }
+    for (; ia < nia; ia += 2) {
+      const uint32_t sa = ia % (uint32_t)NA, pa = ((ia / (uint32_t)NA) & 1) ^ 1;
+      if (tid == 0) tc_trace(g, TC_W_PROD + pg, ia, 0);
+      mbar_wait(emptyA(sa), pa);
+      if (tid == 0) tc_trace(g, TC_W_PROD + pg, ia, 1);
+      uint8_t* dst_hi = smA + sa * a_stage;
+      store_batch(v, pl, dst_hi);
+      if (tid == 0) tc_trace(g, TC_W_PROD + pg, ia, 2);
+      for (int p0 = pl + 16 * TC_PB; p0 < P; p0 += 16 * TC_PB) {   // patches above 192 pixels (7x7)
+        load_batch(v, p0, py, px);
+        store_batch(v, p0, dst_hi);
       }
       fence_async_smem();
-      mbar_arrive(fullA(s));
-    }
-    // ===================== epilogue: TMEM -> registers -> global =====================
-    mbar_wait(accFull, 0);
-    tc_fence_after();
-    const int r = warp * 32 + lane;
-    const int oy = oy0 + (r >> 3), ox = ox0 + (r & 7);
-    const bool ok = oy < d.Ho && ox < d.Wo;
-    const int64_t m = ((int64_t)bimg * d.Ho + oy) * d.Wo + ox;
-    for (int col0 = 0; col0 < g.BN; col0 += 16) {
-      if (n0 + col0 >= d.cout) break;
-      uint32_t v[16];
-      tmem_ld16(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)col0, v);
-      if (ok) {
-#pragma unroll
-        for (int e = 0; e < 16; e += 4)
-          tc_epilogue4(d, m, n0 + col0 + e, __uint_as_float(v[e]), __uint_as_float(v[e + 1]),
-                       __uint_as_float(v[e + 2]), __uint_as_float(v[e + 3]));
+      mbar_arrive(fullA(sa));
+      if (tid == 0) tc_trace(g, TC_W_PROD + pg, ia, 3);
+      if (ia + 2 < nia) {          // prefetch the next stage of this group into registers
+        setup(ia + 2);
+        py = py0; px = px0;
+        load_batch(v, pl, py, px);
       }
     }
-  } else if (warp == 4) {
-    // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(g.BN >> 3) << 17) | (8u << 24);
-      const uint32_t sboA = (uint32_t)g.PW * 16u, lboB = (uint32_t)g.BN * 16u;
-      uint32_t it = 0, acc = 0;
-      for (int gi = 0; gi < g.ngroups; ++gi) {
-        const int s = gi & 1;
-        mbar_wait(fullA(s), (gi >> 1) & 1);
-        tc_fence_after();
-        const int nks = (cin - gi * TC_CG) > 16 ? 2 : 1;
-        const uint32_t a_hi = smem_u32(smA + s * a_stage), a_lo = a_hi + a_part;
-        for (int tap = 0; tap < g.ntaps; ++tap, ++it) {
-          const int ky = tap / d.kw, kx = tap - ky * d.kw;
-          const uint32_t sb = it % g.NB;
-          mbar_wait(fullB(sb), (it / g.NB) & 1);
-          tc_fence_after();
-          const uint32_t b_hi = smem_u32(smB + sb * b_stage), b_lo = b_hi + b_part;
-          const uint32_t toff = (uint32_t)(ky * g.PW + kx) * 16u;
-          for (int ks = 0; ks < nks; ++ks) {
-            const uint64_t dah = make_desc(a_hi + toff + ks * 2 * g.lboA, g.lboA, sboA);
-            const uint64_t dbh = make_desc(b_hi + ks * 2 * lboB, lboB, 128u);
-            tc_mma_bf16(tmem_base, dah, dbh, idesc, acc);
-            acc = 1;
-            if (SPLIT == 3) {
-              const uint64_t dal = make_desc(a_lo + toff + ks * 2 * g.lboA, g.lboA, sboA);
-              const uint64_t dbl = make_desc(b_lo + ks * 2 * lboB, lboB, 128u);
-              tc_mma_bf16(tmem_base, dal, dbh, idesc, 1);
-              tc_mma_bf16(tmem_base, dah, dbl, idesc, 1);
-            }
-          }
-          tc_commit(emptyB(sb));
-        }
-        tc_commit(emptyA(s));
-      }
-      tc_commit(accFull);
-    }
-    __syncwarp();
-  } else {
-    // ===================== weight loader (one thread, bulk async copies) =====================
-    if (lane == 0) {
-      const uint32_t nstage = (uint32_t)g.ngroups * g.ntaps;
-      const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(d.weight) + (size_t)blockIdx.y * nstage * (2u * b_part);
-      for (uint32_t it = 0; it < nstage; ++it) {
-        const uint32_t sb = it % g.NB;
-        mbar_wait(emptyB(sb), ((it / g.NB) & 1) ^ 1);
-        mbar_arrive_expect_tx(fullB(sb), b_stage);
-        bulk_g2s(smem_u32(smB + sb * b_stage), wsrc + (size_t)it * (2u * b_part), b_stage, fullB(sb));
-      }
-    }
-    __syncwarp();
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == TC_W_MMA) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)g.tmem_cols)
                  : "memory");
   }
 }
 
 }  // namespace zt
+
+static long long* g_tc_trace = nullptr;
+static int g_tc_trace_cap = 0;
+// debug: device buffer [1 + 2*cap] int64 (counter, then (tag, ns) pairs) or NULL to disable
+extern "C" int zt_debug_set_tc_trace(void* buf, int cap) {
+  g_tc_trace = (long long*)buf;
+  g_tc_trace_cap = cap;
+  return ZT_OK;
+}
 
 extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stream) {
   using namespace zt;
@@ -339,7 +546,7 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
   if (d.epi == ZT_EPI_GRU_ZR) ZT_REQUIRE(d.aux0 && d.aux1 && (d.cout & 7) == 0, "conv_tc: GRU_ZR needs aux0/aux1 and cout%%8==0");
   if (d.epi == ZT_EPI_GRU_Q) ZT_REQUIRE(d.aux0 && d.aux1, "conv_tc: GRU_Q needs aux0/aux1");
   if (d.epi == ZT_EPI_ADD_RELU || d.epi == ZT_EPI_ADD) ZT_REQUIRE(d.aux0, "conv_tc: residual epilogue needs aux0");
-  ZT_REQUIRE((int64_t)d.B * d.H * d.W < (1ll << 31) && d.B <= 65535, "conv_tc: too many pixels");
+  ZT_REQUIRE((int64_t)d.B * d.H * d.W < (1ll << 31), "conv_tc: too many pixels");
 
   TcGeom g;
   g.BN = BN;
@@ -350,27 +557,67 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
   g.lboA = ceil_div(g.P * 16, 128) * 128 + 32;   // +32 B: conflict-free producer stores
   g.tiles_x = ceil_div(d.Wo, TC_TW);
   g.tiles_y = ceil_div(d.Ho, TC_TH);
+  g.S = g.tiles_x * g.tiles_y * d.B;
+  g.trace = g_tc_trace;
+  g.trace_cap = g_tc_trace_cap;
   g.tmem_cols = 32;
-  while (g.tmem_cols < BN) g.tmem_cols <<= 1;
+  while (g.tmem_cols < 2 * BN) g.tmem_cols <<= 1;
   const int npart = split == 3 ? 2 : 1;
-  const size_t a_bytes = (size_t)TC_NA * 4 * g.lboA * npart;
+  const size_t a_stage = (size_t)4 * g.lboA * npart;
   const size_t b_stage = (size_t)4 * BN * 16 * npart;
-  // aim for <= ~110 KB per CTA so two CTAs share an SM (one's epilogue overlaps the other's MMAs)
-  const size_t budget = 110 * 1024;
-  int nb = a_bytes + 256 < budget ? (int)((budget - a_bytes - 256) / b_stage) : 2;
-  g.NB = nb < 2 ? 2 : (nb > 8 ? 8 : nb);
-  const size_t smem = 256 + a_bytes + (size_t)g.NB * b_stage;
+  const size_t budget = 226 * 1024 - TC_BAR_BYTES - TC_EPI_BYTES;
+  const size_t nstage = (size_t)g.ngroups * g.ntaps;
+  const int n_tiles = ceil_div(d.cout, BN);
+  int gx = kNumSMs / n_tiles;
+  if (gx < 1) gx = 1;
+  if (gx > g.S) gx = g.S;
+  // resident weights pay off when a CTA walks more than one pixel tile
+  g.resident = (nstage * b_stage + 2 * a_stage <= budget && g.S > gx) ? 1 : 0;
+  if (g.resident) {
+    g.NB = (int)nstage;
+    g.NA = (int)((budget - nstage * b_stage) / a_stage);
+  } else {
+    g.NA = (int)(budget / 2 / a_stage);
+    if (g.NA < 2) g.NA = 2;
+  }
+  if (g.NA > 8) g.NA = 8;
+  if (!g.resident) {
+    ZT_REQUIRE((size_t)g.NA * a_stage + 2 * b_stage <= budget, "conv_tc: tile does not fit shared memory");
+    g.NB = (int)((budget - (size_t)g.NA * a_stage) / b_stage);
+    if (g.NB > 32) g.NB = 32;
+    if ((size_t)g.NB > nstage && nstage >= 2) g.NB = (int)nstage;
+  }
+  const size_t smem = TC_BAR_BYTES + TC_EPI_BYTES + (size_t)g.NA * a_stage + (size_t)g.NB * b_stage;
   ZT_REQUIRE(smem <= 227 * 1024, "conv_tc: tile needs %zu B of shared memory", smem);
 
-  static bool attr_done = false;
-  if (!attr_done) {
-    ZT_CUDA(cudaFuncSetAttribute(conv_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    ZT_CUDA(cudaFuncSetAttribute(conv_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_done = true;
-  }
-  dim3 grid(g.tiles_x * g.tiles_y, ceil_div(d.cout, BN), d.B);
+  dim3 grid(gx, n_tiles, 1);
   cudaStream_t st = (cudaStream_t)stream;
-  if (split == 3) conv_tc_kernel<3><<<grid, TC_THREADS, smem, st>>>(d, g);
-  else conv_tc_kernel<1><<<grid, TC_THREADS, smem, st>>>(d, g);
+#define ZT_TC_LAUNCH(SP, EP, AC)                                                                          \
+  do {                                                                                                    \
+    static bool attr_done = false;                                                                        \
+    if (!attr_done) {                                                                                     \
+      ZT_CUDA(cudaFuncSetAttribute(conv_tc_kernel<SP, EP, AC>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                   227 * 1024));                                                          \
+      attr_done = true;                                                                                   \
+    }                                                                                                     \
+    conv_tc_kernel<SP, EP, AC><<<grid, TC_THREADS, smem, st>>>(d, g);                                     \
+  } while (0)
+#define ZT_TC_CASE(EP, AC)                                  \
+  if (d.epi == (EP) && ((AC) < 0 || d.act == (AC))) {       \
+    if (split == 3) ZT_TC_LAUNCH(3, EP, AC);                \
+    else ZT_TC_LAUNCH(1, EP, AC);                           \
+    return check_launch("conv_tc_kernel");                  \
+  }
+  ZT_TC_CASE(ZT_EPI_PLAIN, ZT_ACT_RELU)
+  ZT_TC_CASE(ZT_EPI_PLAIN, ZT_ACT_NONE)
+  ZT_TC_CASE(ZT_EPI_PLAIN, ZT_ACT_LRELU02)
+  ZT_TC_CASE(ZT_EPI_PLAIN, ZT_ACT_SIGMOID)
+  ZT_TC_CASE(ZT_EPI_PLAIN, ZT_ACT_TANH)
+  ZT_TC_CASE(ZT_EPI_GRU_ZR, -1)
+  ZT_TC_CASE(ZT_EPI_GRU_Q, -1)
+  ZT_TC_CASE(ZT_EPI_ADD_RELU, ZT_ACT_RELU)
+  ZT_TC_CASE(ZT_EPI_ADD, ZT_ACT_RELU)
+  if (split == 3) ZT_TC_LAUNCH(3, -1, -1);
+  else ZT_TC_LAUNCH(1, -1, -1);
   return check_launch("conv_tc_kernel");
 }
