@@ -70,8 +70,9 @@ typedef struct ZtConv {
 int zt_conv2d_nhwc_f32(const ZtConv* d, void* stream);
 
 /* Same convolution on the tcgen05 tensor cores (stride 1 only): `weight` points at bf16 hi/lo
- * weights packed by the host as [n_tile][32-ch group][tap][hi|lo][k-chunk 4][row BN][8]
- * (zero padded); w_cs is ignored.  split = 1: bf16 x bf16; split = 3: hi*hi + lo*hi + hi*lo
+ * weights packed by the host as [n_tile][64-ch group][tap][hi|lo][row BN][64 ch], every
+ * 128-byte row stored with the UMMA 128B swizzle (16 B chunk c of row n at position c^(n&7)),
+ * zero padded; w_cs is ignored.  split = 1: bf16 x bf16; split = 3: hi*hi + lo*hi + hi*lo
  * (about 2^-16 relative, needed for RAFT's 0.01 px tolerance).  BN = N tile, multiple of 16
  * in [16,256].  Same call sites as zt_conv2d_nhwc_f32. */
 int zt_conv2d_tc_nhwc(const ZtConv* d, int BN, int split, void* stream);

@@ -4,9 +4,12 @@
 // K = taps * cin.  Activations stay fp32 NHWC in HBM (the layout every other kernel of the
 // path uses); producer warps load the input patch INCLUDING its halo once per 32-channel
 // group, split every value into bf16 hi + bf16 lo and store both in shared memory in the
-// UMMA no-swizzle K-major canonical layout [k-chunk(8ch)][patch pixel][16 B].  Every filter
-// tap is then just a *shifted view* of the same patch: the A-operand shared-memory
-// descriptor starts at pixel (ky,kx) of the patch and uses SBO = patch-row pitch, so the
+// UMMA 128-byte-swizzle K-major layout: one 128 B row (64 channels) per patch pixel, 16 B
+// chunk c of row p stored at chunk position c ^ (p & 7).  (The no-swizzle layout works too
+// but is fetched at ~16 B/clk: measured ~210 clk per M128 K16 MMA.)  Every filter tap is
+// just a *shifted view* of the same patch: the A-operand shared-memory descriptor starts at
+// pixel (ky,kx) of the patch and uses SBO = patch-row pitch; the hardware swizzle is a
+// function of the absolute shared-memory address, so any row offset stays consistent.  The
 // 9 (or 5, 25, 49) taps re-use one copy of the data (no im2col, no re-reads).
 // Weights are pre-packed on the host (bf16 hi/lo, canonical layout) and streamed per
 // (channel group, tap) with cp.async.bulk + mbarrier complete_tx.
@@ -19,13 +22,14 @@
 // Replaces nn.Conv2d call sites with stride 1: model/model.py:24-28,40-44,74-81;
 // model/RAFT/update.py:13-14,45-60,89-97,127-136; model/RAFT/extractor.py:46-55,167-191.
 #include <cuda_bf16.h>
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace zt {
 
 constexpr int TC_TW = 8;          // tile width in pixels (= one 8-row core-matrix group)
 constexpr int TC_TH = 16;         // tile height -> 128 GEMM rows
-constexpr int TC_CG = 32;         // channels per A stage (4 chunks of 8)
+constexpr int TC_CG = 64;         // channels per A stage: one 128 B swizzled row per pixel
 // warps 0-7 epilogue (warp%4 = TMEM lane quadrant, warp/4 = odd/even 16-column groups),
 // 8 MMA issuer, 9 weight loader, 10-13 producer group 0, 14-17 producer group 1
 // (the producer groups alternate A stages)
@@ -38,10 +42,10 @@ constexpr int TC_EPI_BYTES = 8 * 32 * TC_EPI_LD * 4;        // 8 epilogue warps 
 
 struct TcGeom {
   int BN;            // N tile (multiple of 16, <= 256)
-  int ngroups;       // ceil(cin / 32)
+  int ngroups;       // ceil(cin / 64)
   int ntaps;         // kh*kw
   int PW, P;         // patch width, patch pixels
-  int lboA;          // bytes between k-chunks of the A patch
+  int a_part;        // bytes of one (hi or lo) patch: P*128 rounded up to 1024
   int tiles_x, tiles_y;
   int NA;            // A (patch) ring depth
   int NB;            // weight ring depth (resident: number of weight stages = ngroups*ntaps)
@@ -52,18 +56,25 @@ struct TcGeom {
   int trace_cap;
 };
 
-// debug timeline: record (role, tile/stage index, event, globaltimer ns) for CTA (0,0)
-__device__ __forceinline__ void tc_trace(const TcGeom& g, int role, int idx, int ev) {
-  if (g.trace && blockIdx.x == 0 && blockIdx.y == 0) {
-    long long tns;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tns));
-    const int slot = (int)atomicAdd(reinterpret_cast<unsigned long long*>(g.trace), 1ull);
-    if (slot < g.trace_cap) {
-      g.trace[1 + 2 * slot] = ((long long)role << 48) | ((long long)ev << 32) | (unsigned)idx;
-      g.trace[2 + 2 * slot] = tns;
+// debug timeline: record (event, index, globaltimer ns) for CTA (0,0); every role (warp) owns a
+// region of trace_cap entries and a private counter, so tracing costs one fire-and-forget store
+struct TcTracer {
+  long long* base;
+  int n, cap;
+  __device__ __forceinline__ TcTracer(const TcGeom& g, int role)
+      : base(nullptr), n(0), cap(g.trace_cap) {
+    if (g.trace && blockIdx.x == 0 && blockIdx.y == 0) base = g.trace + (size_t)role * 2 * g.trace_cap;
+  }
+  __device__ __forceinline__ void operator()(int idx, int ev) {
+    if (base && n < cap) {
+      long long tns;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tns));
+      base[2 * n] = ((long long)(ev + 1) << 32) | (unsigned)idx;
+      base[2 * n + 1] = tns;
+      ++n;
     }
   }
-}
+};
 
 // ---------------------------------------------------------------- PTX helpers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -104,10 +115,30 @@ __device__ __forceinline__ void tc_mma_bf16(uint32_t tmem_d, uint64_t da, uint64
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
 }
-// shared-memory matrix descriptor, no swizzle, K-major: ((8,m),2):((16B,SBO),LBO)
-__device__ __forceinline__ uint64_t make_desc(uint32_t addr, uint32_t lbo, uint32_t sbo) {
-  return (uint64_t)((addr >> 4) & 0x3FFF) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) |
-         ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) | (1ull << 46);
+// One lane of a fully converged warp.  The MMA warp runs its loops with all 32 lanes and elects
+// one only around the tcgen05 instructions: descriptors then stay provably warp-uniform (no
+// per-lane "waterfall" loops moving them into uniform registers - that cost ~230 clk per MMA).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+// same MMA with the descriptors given as (lo, hi) words: only the lo word (start address) varies
+__device__ __forceinline__ void tc_mma_bf16_lh(uint32_t tmem_d, uint32_t alo, uint32_t ahi, uint32_t blo, uint32_t bhi,
+                                               uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "mov.b64 da, {%1, %2};\n\t"
+      "mov.b64 db, {%3, %4};\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}"
+      ::"r"(tmem_d), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc), "r"(acc) : "memory");
+}
+// shared-memory matrix descriptor, SWIZZLE_128B, K-major: rows of 128 B, 8-row groups SBO apart
+// (LBO is unused for a K extent inside one swizzle atom; CUTLASS encodes 1)
+__device__ __forceinline__ uint64_t make_desc(uint32_t addr, uint32_t sbo) {
+  return (uint64_t)((addr >> 4) & 0x3FFF) | (1ull << 16) | ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) |
+         (1ull << 46) | (2ull << 61);
 }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
   asm volatile(
@@ -205,12 +236,13 @@ __device__ __forceinline__ void tc_epilogue4(const ZtConv& d, int64_t m, int nb,
 // overlaps the MMAs of tile i+1; small weight sets stay resident in shared memory.
 template <int SPLIT, int EPI_T, int ACT_T>
 __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, const TcGeom g) {
-  extern __shared__ __align__(128) uint8_t smem[];
+  extern __shared__ __align__(1024) uint8_t smem[];
   constexpr int NPART = SPLIT == 3 ? 2 : 1;
+  if ((smem_u32(smem) & 1023u) != 0) __trap();     // swizzle atoms need 1024 B alignment
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TC_BAR_BYTES - 16);
-  const uint32_t a_part = 4u * g.lboA, a_stage = a_part * NPART;
-  const uint32_t b_part = 4u * g.BN * 16u, b_stage = b_part * NPART;
-  uint8_t* smA = smem + TC_BAR_BYTES + TC_EPI_BYTES;
+  const uint32_t a_part = (uint32_t)g.a_part, a_stage = a_part * NPART;
+  const uint32_t b_part = (uint32_t)g.BN * 128u, b_stage = b_part * NPART;
+  uint8_t* smA = smem + TC_BAR_BYTES + TC_EPI_BYTES;   // 1024 B aligned (swizzle atoms)
   uint8_t* smB = smA + g.NA * a_stage;
   const uint32_t bar0 = smem_u32(smem);
   const int NA = g.NA, NB = g.NB;
@@ -259,6 +291,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
     const int epi = EPI_T >= 0 ? EPI_T : d.epi;
     const int Ch = d.cout >> 1;
     uint32_t lt = 0;
+    TcTracer trace(g, warp);
     for (int t = blockIdx.x; t < S; t += gridDim.x, ++lt) {
       const int bimg = t / tiles_per_img, tr = t - bimg * tiles_per_img;
       const int tyi = tr / g.tiles_x, txi = tr - tyi * g.tiles_x;
@@ -289,11 +322,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
         float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
         if (d.bias && nvalid > 0) bv = ld4_or_scalar(d.bias + nb, nvalid);
         if (!waited) {
-          if (lane == 0) tc_trace(g, warp, lt, 0);
+          if (lane == 0) trace(lt, 0);
           mbar_wait(accFull(buf), (lt >> 1) & 1);
           tc_fence_after();
           waited = true;
-          if (lane == 0) tc_trace(g, warp, lt, 1);
+          if (lane == 0) trace(lt, 1);
         }
         const uint32_t taddr = tmem_base + buf * (uint32_t)g.BN + ((uint32_t)(quad * 32) << 16) + (uint32_t)(ch * 32);
         uint32_t v[16];
@@ -322,83 +355,95 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
       if (!waited) { mbar_wait(accFull(buf), (lt >> 1) & 1); tc_fence_after(); }
       tc_fence_before();
       mbar_arrive(accEmpty(buf));
-      if (lane == 0) tc_trace(g, warp, lt, 2);
+      if (lane == 0) trace(lt, 2);
     }
   } else if (warp == TC_W_MMA) {
-    // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (whole warp converged, one elected lane issues) ==========
+    {
       const uint32_t BN = g.BN, PW = g.PW, kh = d.kh, kw = d.kw;
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((BN >> 3) << 17) | (8u << 24);
-      const uint32_t lboA = g.lboA, lboB = BN * 16u;
-      // descriptor templates: only the 14-bit start-address field (16 B units) changes per MMA
-      const uint64_t descA0 = make_desc(0, lboA, PW * 16u), descB0 = make_desc(0, lboB, 128u);
-      const uint32_t ksA = (2u * lboA) >> 4, ksB = (2u * lboB) >> 4;
+      // descriptor templates: only the 14-bit start-address field (16 B units) changes per MMA;
+      // a K step of 16 channels is +32 B inside the swizzled 128 B row
+      const uint64_t descA0 = make_desc(0, PW * 128u), descB0 = make_desc(0, 1024u);
       const uint32_t apart16 = a_part >> 4, bpart16 = b_part >> 4;
       const uint32_t smA16 = smem_u32(smA) >> 4, smB16 = smem_u32(smB) >> 4;
       const uint32_t a_stage16 = a_stage >> 4, b_stage16 = b_stage >> 4;
       const bool resident = g.resident != 0;
-      uint32_t ia = 0, ib = 0, lt = 0;
+      uint32_t lt = 0;
+      TcTracer trace(g, TC_W_MMA);
       uint32_t sa = 0, pa = 0;          // A ring slot / parity
       uint32_t sbr = 0, pb = 0;         // B ring slot / parity (streamed mode)
       if (resident) { mbar_wait(fullB(0), 0); tc_fence_after(); }
       for (int t = blockIdx.x; t < S; t += gridDim.x, ++lt) {
         const uint32_t buf = lt & 1;
-        tc_trace(g, TC_W_MMA, lt, 3);
+        if (lane == 0) trace(lt, 3);
         mbar_wait(accEmpty(buf), ((lt >> 1) & 1) ^ 1);
         tc_fence_after();
-        tc_trace(g, TC_W_MMA, lt, 4);
+        if (lane == 0) trace(lt, 4);
         const uint32_t tmem_d = tmem_base + buf * BN;
         uint32_t acc = 0;
         int crem = cin;
         uint32_t bres16 = smB16;        // resident mode: walks the weight stages in order
         for (int gi = 0; gi < ngroups; ++gi, crem -= TC_CG) {
-          tc_trace(g, TC_W_MMA, lt * ngroups + gi, 0);
+          if (lane == 0) trace(lt * ngroups + gi, 0);
           mbar_wait(fullA(sa), pa);
           tc_fence_after();
-          tc_trace(g, TC_W_MMA, lt * ngroups + gi, 1);
-          const bool two = crem > 16;
-          const uint32_t a16 = smA16 + sa * a_stage16;
-          uint32_t row16 = a16;
-          for (uint32_t ky = 0; ky < kh; ++ky, row16 += PW) {
-            for (uint32_t kx = 0; kx < kw; ++kx) {
-              uint32_t b16;
-              if (resident) {
-                b16 = bres16;
-                bres16 += b_stage16;
-              } else {
-                mbar_wait(fullB(sbr), pb);
-                tc_fence_after();
-                b16 = smB16 + sbr * b_stage16;
-              }
-              const uint64_t dah = descA0 + (row16 + kx), dbh = descB0 + b16;
-              tc_mma_bf16(tmem_d, dah, dbh, idesc, acc);
-              acc = 1;
-              if (SPLIT == 3) {
-                tc_mma_bf16(tmem_d, dah + apart16, dbh, idesc, 1);
-                tc_mma_bf16(tmem_d, dah, dbh + bpart16, idesc, 1);
-              }
-              if (two) {
-                tc_mma_bf16(tmem_d, dah + ksA, dbh + ksB, idesc, 1);
-                if (SPLIT == 3) {
-                  tc_mma_bf16(tmem_d, dah + ksA + apart16, dbh + ksB, idesc, 1);
-                  tc_mma_bf16(tmem_d, dah + ksA, dbh + ksB + bpart16, idesc, 1);
+          if (lane == 0) trace(lt * ngroups + gi, 1);
+          const int nks = crem >= TC_CG ? 4 : (crem + 15) >> 4;
+          // one elected lane issues the whole stage: lean loop, descriptors as 32-bit lo words
+          if (elect_one()) {
+            const uint32_t ahi = (uint32_t)(descA0 >> 32), bhi = (uint32_t)(descB0 >> 32);
+            uint32_t rowlo = (uint32_t)descA0 + smA16 + sa * a_stage16;
+            const uint32_t blo0 = (uint32_t)descB0;
+            for (uint32_t ky = 0; ky < kh; ++ky, rowlo += PW * 8u) {
+              uint32_t alo = rowlo;
+              for (uint32_t kx = 0; kx < kw; ++kx, alo += 8u) {
+                uint32_t blo;
+                if (resident) {
+                  blo = blo0 + bres16;
+                  bres16 += b_stage16;
+                } else {
+                  mbar_wait(fullB(sbr), pb);
+                  tc_fence_after();
+                  blo = blo0 + smB16 + sbr * b_stage16;
                 }
-              }
-              if (!resident) {
-                tc_commit(emptyB(sbr));
-                if (++sbr == (uint32_t)NB) { sbr = 0; pb ^= 1; }
+                if (nks == 4) {
+#pragma unroll
+                  for (uint32_t ks = 0; ks < 4; ++ks) {
+                    tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc, ks == 0 ? acc : 1u);
+                    if (SPLIT == 3) {
+                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks + apart16, ahi, blo + 2 * ks, bhi, idesc, 1);
+                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks + bpart16, bhi, idesc, 1);
+                    }
+                  }
+                } else {
+                  for (int ks = 0; ks < nks; ++ks) {
+                    tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc, ks == 0 ? acc : 1u);
+                    if (SPLIT == 3) {
+                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks + apart16, ahi, blo + 2 * ks, bhi, idesc, 1);
+                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks + bpart16, bhi, idesc, 1);
+                    }
+                  }
+                }
+                acc = 1;
+                if (!resident) {
+                  tc_commit(emptyB(sbr));
+                  if (++sbr == (uint32_t)NB) { sbr = 0; pb ^= 1; }
+                }
               }
             }
           }
-          tc_commit(emptyA(sa));
-          tc_trace(g, TC_W_MMA, lt * ngroups + gi, 2);
+          // (acc, bres16, sbr, pb live in the elected lane only: elect.sync always picks the same lane)
+          __syncwarp();
+          if (elect_one()) tc_commit(emptyA(sa));
+          __syncwarp();
+          if (lane == 0) trace(lt * ngroups + gi, 2);
           if (++sa == (uint32_t)NA) { sa = 0; pa ^= 1; }
         }
-        tc_commit(accFull(buf));
+        if (elect_one()) tc_commit(accFull(buf));
+        __syncwarp();
       }
-      (void)ia; (void)ib;
     }
-    __syncwarp();
   } else if (warp == TC_W_LOAD) {
     // ===================== weight loader (one thread, bulk async copies) =====================
     if (lane == 0) {
@@ -429,9 +474,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
     // wait for the MMAs that free the slot.
     const int pg = (warp - TC_W_PROD) >> 2;                      // producer group 0 / 1
     const int tid = threadIdx.x - TC_W_PROD * 32 - pg * 128;     // 0..127 within the group
-    const int q = tid & 7, pl = tid >> 3;
+    const int q = tid & 15, pl = tid >> 4;          // 16 float4 pieces per pixel, 8 pixels per pass
     const int P = g.P, PW = g.PW;
-    const uint32_t soff = (uint32_t)(q >> 1) * g.lboA + (uint32_t)(q & 1) * 8u;
     const int py0 = pl / PW, px0 = pl - py0 * PW;
     const int ntl = S > (int)blockIdx.x ? (S - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
     const uint32_t nia = (uint32_t)ntl * ngroups;
@@ -460,24 +504,26 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
     auto load_batch = [&](float4 (&v)[TC_PB], int p0, int& py, int& px) {
 #pragma unroll
       for (int u = 0; u < TC_PB; ++u) {
-        const int p = p0 + 16 * u;
+        const int p = p0 + 8 * u;
         const int iy = iy0 + py, ix = ix0 + px;
         v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (cvalid && p < P && iy >= 0 && iy < d.H && ix >= 0 && ix < d.W)
           v[u] = __ldg(reinterpret_cast<const float4*>(src + (img_pix + (int64_t)iy * d.W + ix) * cs));
-        px += 16;
+        px += 8;
         while (px >= PW) { px -= PW; ++py; }
       }
     };
     auto store_batch = [&](const float4 (&v)[TC_PB], int p0, uint8_t* dst_hi) {
 #pragma unroll
       for (int u = 0; u < TC_PB; ++u) {
-        const int p = p0 + 16 * u;
+        const int p = p0 + 8 * u;
         if (p < P) {
           uint2 hi, lo;
           split4(v[u], hi, lo);
-          *reinterpret_cast<uint2*>(dst_hi + soff + (uint32_t)p * 16u) = hi;
-          if (SPLIT == 3) *reinterpret_cast<uint2*>(dst_hi + a_part + soff + (uint32_t)p * 16u) = lo;
+          // 128B swizzle: 16 B chunk (q>>1) of row p lives at chunk position (q>>1) ^ (p & 7)
+          const uint32_t off = (uint32_t)p * 128u + ((uint32_t)((q >> 1) ^ (p & 7)) << 4) + (uint32_t)(q & 1) * 8u;
+          *reinterpret_cast<uint2*>(dst_hi + off) = hi;
+          if (SPLIT == 3) *reinterpret_cast<uint2*>(dst_hi + a_part + off) = lo;
         }
       }
     };
@@ -485,22 +531,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
     float4 v[TC_PB];
     int py = py0, px = px0;
     uint32_t ia = pg;
+    TcTracer trace(g, TC_W_PROD + pg);
     if (ia < nia) { setup(ia); load_batch(v, pl, py, px); }
     for (; ia < nia; ia += 2) {
       const uint32_t sa = ia % (uint32_t)NA, pa = ((ia / (uint32_t)NA) & 1) ^ 1;
-      if (tid == 0) tc_trace(g, TC_W_PROD + pg, ia, 0);
+      if (tid == 0) trace(ia, 0);
       mbar_wait(emptyA(sa), pa);
-      if (tid == 0) tc_trace(g, TC_W_PROD + pg, ia, 1);
+      if (tid == 0) trace(ia, 1);
       uint8_t* dst_hi = smA + sa * a_stage;
       store_batch(v, pl, dst_hi);
-      if (tid == 0) tc_trace(g, TC_W_PROD + pg, ia, 2);
-      for (int p0 = pl + 16 * TC_PB; p0 < P; p0 += 16 * TC_PB) {   // patches above 192 pixels (7x7)
+      if (tid == 0) trace(ia, 2);
+      for (int p0 = pl + 8 * TC_PB; p0 < P; p0 += 8 * TC_PB) {   // rest of the patch (96 pixels per batch)
         load_batch(v, p0, py, px);
         store_batch(v, p0, dst_hi);
       }
       fence_async_smem();
       mbar_arrive(fullA(sa));
-      if (tid == 0) tc_trace(g, TC_W_PROD + pg, ia, 3);
+      if (tid == 0) trace(ia, 3);
       if (ia + 2 < nia) {          // prefetch the next stage of this group into registers
         setup(ia + 2);
         py = py0; px = px0;
@@ -554,7 +601,7 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
   g.ntaps = d.kh * d.kw;
   g.PW = TC_TW + d.kw - 1;
   g.P = (TC_TH + d.kh - 1) * g.PW;
-  g.lboA = ceil_div(g.P * 16, 128) * 128 + 32;   // +32 B: conflict-free producer stores
+  g.a_part = ceil_div(g.P * 128, 1024) * 1024;
   g.tiles_x = ceil_div(d.Wo, TC_TW);
   g.tiles_y = ceil_div(d.Ho, TC_TH);
   g.S = g.tiles_x * g.tiles_y * d.B;
@@ -563,8 +610,8 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
   g.tmem_cols = 32;
   while (g.tmem_cols < 2 * BN) g.tmem_cols <<= 1;
   const int npart = split == 3 ? 2 : 1;
-  const size_t a_stage = (size_t)4 * g.lboA * npart;
-  const size_t b_stage = (size_t)4 * BN * 16 * npart;
+  const size_t a_stage = (size_t)g.a_part * npart;
+  const size_t b_stage = (size_t)BN * 128 * npart;
   const size_t budget = 226 * 1024 - TC_BAR_BYTES - TC_EPI_BYTES;
   const size_t nstage = (size_t)g.ngroups * g.ntaps;
   const int n_tiles = ceil_div(d.cout, BN);
@@ -579,10 +626,11 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
   } else {
     g.NA = (int)(budget / 2 / a_stage);
     if (g.NA < 2) g.NA = 2;
+    if ((size_t)g.NA * a_stage + 2 * b_stage > budget) g.NA = 1;   // huge patches (7x7 hi+lo): no overlap
   }
   if (g.NA > 8) g.NA = 8;
   if (!g.resident) {
-    ZT_REQUIRE((size_t)g.NA * a_stage + 2 * b_stage <= budget, "conv_tc: tile does not fit shared memory");
+    ZT_REQUIRE((size_t)g.NA * a_stage + b_stage <= budget, "conv_tc: tile does not fit shared memory");
     g.NB = (int)((budget - (size_t)g.NA * a_stage) / b_stage);
     if (g.NB > 32) g.NB = 32;
     if ((size_t)g.NB > nstage && nstage >= 2) g.NB = (int)nstage;

@@ -55,19 +55,25 @@ class ConvW:
 
     def tc_pack(self, BN):
         """bf16 hi/lo weights in the tcgen05 kernel's layout (csrc/conv_tc.cu):
-        [n_tile][32-channel group][tap][hi|lo][k-chunk 4][row BN][8] - one contiguous block per
-        (n_tile, group, tap) = one cp.async.bulk per weight-ring stage."""
+        [n_tile][64-channel group][tap][hi|lo][row BN][128 B], each 128 B row (64 input channels
+        of one tap) stored with the UMMA 128-byte swizzle (16 B chunk c of row n at chunk
+        position c ^ (n & 7)) - one contiguous block per (n_tile, group, tap) = one
+        cp.async.bulk per weight stage."""
         t = self._tc.get(BN)
         if t is None:
             w = self.w_raw
             cout, cin, kh, kw = w.shape
-            ng, nt = (self.cin + 31) // 32, (cout + BN - 1) // BN
-            wp = torch.zeros(nt * BN, ng * 32, kh, kw, device=w.device, dtype=torch.float32)
+            ng, nt = (self.cin + 63) // 64, (cout + BN - 1) // BN
+            wp = torch.zeros(nt * BN, ng * 64, kh, kw, device=w.device, dtype=torch.float32)
             wp[:cout, :cin] = w
             hi = wp.to(torch.bfloat16)
             lo = (wp - hi.float()).to(torch.bfloat16)
-            x = torch.stack([hi, lo], 0).reshape(2, nt, BN, ng, 4, 8, kh * kw)
-            t = x.permute(1, 3, 6, 0, 4, 2, 5).contiguous()
+            x = torch.stack([hi, lo], 0).reshape(2, nt, BN, ng, 8, 8, kh * kw)
+            x = x.permute(1, 3, 6, 0, 2, 4, 5).contiguous()      # nt, g, tap, part, row, chunk, e
+            n = torch.arange(BN, device=w.device)
+            src = torch.arange(8, device=w.device)[None, :] ^ (n[:, None] & 7)   # position j <- chunk j^(n&7)
+            idx = src.view(1, 1, 1, 1, BN, 8, 1).expand_as(x)
+            t = torch.gather(x, 5, idx).contiguous()
             self._tc[BN] = t
         return t
 
