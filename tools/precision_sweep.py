@@ -27,9 +27,10 @@ if __name__ == "__main__":
         sys.exit(0)
     import torch
     H, W, n = sys.argv[1:4]
-    modes = {"ref": dict(RAFT=0, D1=0, ENH=0, D2=0), "all3": dict(RAFT=3, D1=3, ENH=3, D2=3),
-             "enh1": dict(RAFT=3, D1=3, ENH=1, D2=3), "enh1_d21": dict(RAFT=3, D1=3, ENH=1, D2=1),
-             "nets1": dict(RAFT=3, D1=1, ENH=1, D2=1), "all1": dict(RAFT=1, D1=1, ENH=1, D2=1)}
+    modes = {"ref": dict(RAFT=0, D1=0, ENH=0, D2=0), "nets1": dict(RAFT=3, D1=1, ENH=1, D2=1),
+             "upd1": dict(RAFT=3, RAFT_UPD=1, D1=1, ENH=1, D2=1), "enc1": dict(RAFT=3, RAFT_ENC=1, D1=1, ENH=1, D2=1),
+             "head1": dict(RAFT=3, RAFT_HEAD=1, D1=1, ENH=1, D2=1),
+             "upd_head1": dict(RAFT=3, RAFT_UPD=1, RAFT_HEAD=1, D1=1, ENH=1, D2=1)}
     for name, env in modes.items():
         e = dict(os.environ); e.update({"ZT_TC_" + k: str(v) for k, v in env.items()})
         subprocess.run([sys.executable, __file__, H, W, n, name], env=e, check=True)

@@ -49,6 +49,9 @@ class RaftEngine:
     """RAFT.forward (model/RAFT/raft.py:77-130) on the kernels in csrc/."""
 
     TC = _tc_mode("RAFT", 3)
+    TC_ENC = _tc_mode("RAFT_ENC", TC)      # fnet / cnet
+    TC_UPD = _tc_mode("RAFT_UPD", TC)      # motion encoder + GRU
+    TC_HEAD = _tc_mode("RAFT_HEAD", TC)    # flow head + mask head
 
     def __init__(self, raft):
         self.raft = raft
@@ -103,7 +106,7 @@ class RaftEngine:
 
     # ---- encoders (extractor.py:167-191) ----
     def _encoder(self, enc, x, B, H, W, is_bn):
-        w, ws, T = self.w, self.ws, self.TC
+        w, ws, T = self.w, self.ws, self.TC_ENC
         stats = ws.get("in_stats", (B * 128 * 2,), torch.float64)
         h, wd = H // 2, W // 2
 
@@ -149,7 +152,7 @@ class RaftEngine:
         Returns flow_up NCHW [1,2,hp,wp] (a workspace tensor, valid until the next call)."""
         _dev_check(x2)
         self._prepare(x2.device)
-        w, ws, T = self.w, self.ws, self.TC
+        w, ws, T, TH = self.w, self.ws, self.TC_ENC, self.TC_HEAD
         assert hp % 8 == 0 and wp % 8 == 0
         h8, w8 = hp // 8, wp // 8
         N = h8 * w8
@@ -199,6 +202,7 @@ class RaftEngine:
         fhid = ws.get("fhid", (N, 256))
         delta = ws.get("delta", (N, 4), zero=True)
         ops.flow_update(coords1, None, 0, flow4, 4, hx, 384, 382, h8, w8)
+        T = self.TC_UPD
         for it in range(iters):
             ops.corr_lookup(lv, hs, wsz, coords1, corr, 324, N)
             ops.conv2d(w["enc.convc1"], corr, 324, 324, 1, h8, w8, c1, 256, act="relu", tc=T, bn=64)
@@ -211,14 +215,14 @@ class RaftEngine:
                            aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128, tc=T, bn=64)
                 ops.conv2d(w["gru.q" + s], rh, 128, 128, 1, h8, w8, hx, 384, in1=hx, in1_cs=384, c1=256,
                            in1_off=128, pad=pad, epi="gru_q", aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128, tc=T, bn=32)
-            ops.conv2d(w["fh1"], hx, 384, 128, 1, h8, w8, fhid, 256, pad=(1, 1), act="relu", tc=T, bn=64)
-            ops.conv2d(w["fh2"], fhid, 256, 256, 1, h8, w8, delta, 4, pad=(1, 1), tc=T)
+            ops.conv2d(w["fh1"], hx, 384, 128, 1, h8, w8, fhid, 256, pad=(1, 1), act="relu", tc=TH, bn=64)
+            ops.conv2d(w["fh2"], fhid, 256, 256, 1, h8, w8, delta, 4, pad=(1, 1), tc=TH)
             ops.flow_update(coords1, delta, 4, flow4, 4, hx, 384, 382, h8, w8)
         # convex upsampling mask only for the returned (last) prediction (raft.py:122-130, Q15)
         mh = ws.get("maskh", (N, 256))
         mask = ws.get("mask", (N, 576))
-        ops.conv2d(w["mask0"], hx, 384, 128, 1, h8, w8, mh, 256, pad=(1, 1), act="relu", tc=T, bn=64)
-        ops.conv2d(w["mask2"], mh, 256, 256, 1, h8, w8, mask, 576, scale=0.25, tc=T, bn=64)
+        ops.conv2d(w["mask0"], hx, 384, 128, 1, h8, w8, mh, 256, pad=(1, 1), act="relu", tc=TH, bn=64)
+        ops.conv2d(w["mask2"], mh, 256, 256, 1, h8, w8, mask, 576, scale=0.25, tc=TH, bn=64)
         flow_up = ws.get("flow_up", (1, 2, hp, wp))
         ops.convex_upsample(flow4, 4, mask, 576, flow_up, h8, w8)
         self.last = dict(fmap=fmap, levels=lv, hs=hs, ws=wsz, flow4=flow4, hx=hx, corr=corr, N=N, h8=h8, w8=w8)
