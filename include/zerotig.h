@@ -148,6 +148,43 @@ int zt_retinex_h5_f32(const float* H2, const float* s2, const float* d, int d_cs
 /* save_images quantisation, predict.py:57-61: clip(x*255,0,255) -> uint8 (truncate), HWC */
 int zt_quantize_u8_hwc(const float* x, uint8_t* out, int C, int64_t HW, void* stream);
 
+/* ---- training path: Network.forward (model/model.py:144-203) and loss.py -------------------
+ * NCHW fp32, batch 1.  Reduction entry points ADD raw sums into fp64 accumulators the caller
+ * zeroes; the host turns them into the 17 weighted terms of LossFunction.forward. */
+/* BatchNorm2d in train mode fused with ReLU and the Enhancer residual (model.py:76-78):
+ * out = res + relu(gamma*(x-mean)/sqrt(var+eps)+beta) with batch stats over HW; optionally updates
+ * running_mean/var (momentum, unbiased var).  stats: fp64 scratch [C][2]. */
+int zt_bn_train_nhwc_f32(const float* x, int x_cs, float* out, int out_cs, const float* res, int res_cs,
+                         double* stats, const float* gamma, const float* beta, float* running_mean,
+                         float* running_var, int HW, int C, float eps, float momentum, void* stream);
+/* pair_downsampler utils/utils.py:15-24 on (in + add): out1 = anti-diagonal mean, out2 = diagonal mean */
+int zt_pair_downsample_f32(const float* in, float* out1, float* out2, int C, int H, int W, float add, void* stream);
+/* out[c][p] = (a[c][p] + add) - d[p][c]  (d NHWC), optionally clamped: L_pred / L2 (model.py:149-152) */
+int zt_sub_clamp_f32(const float* a, float add, const float* d, int d_cs, float* out, int C, int64_t HW,
+                     float lo, float hi, int do_clamp, void* stream);
+/* out = clamp((a + add) / b, lo, hi): H2, H11, H12, H1 (model.py:170-177,198-199) */
+int zt_div_clamp_f32(const float* a, float add, const float* b, float* out, int64_t n, float lo, float hi,
+                     void* stream);
+/* TextureDifference.forward loss.py:106-136: 3-plane images -> binary map [H][W] */
+int zt_texture_diff_f32(const float* img1, const float* img2, float* out, int H, int W, void* stream);
+/* utils.blur (utils.py:52-58): reflect pad 10 + 21x21 kernel, run separably; taps = 21 HOST floats */
+int zt_blur21_f32(const float* in, float* tmp, float* out, const float* taps, int C, int H, int W, void* stream);
+/* loss.py:26-47: acc[0] += sum (s2-bright)^2, acc[1] += sum (norm_ll-adj)^2; chansum = fp64[3] scratch */
+int zt_loss_illum_f32(const float* L2, const float* s2, int is_WB, int64_t HW, double* chansum, double* acc,
+                      void* stream);
+/* SmoothLoss loss.py:173-311: acc[0..11] += raw sums of the 12 unique offsets; ycc = 3*H*W scratch */
+int zt_loss_smooth_f32(const float* L2, const float* s2, float* ycc, int H, int W, double* acc, void* stream);
+/* L_TV loss.py:139-152: acc[0] += vertical, acc[1] += horizontal squared differences */
+int zt_loss_tv_f32(const float* x, int C, int H, int W, double* acc, void* stream);
+/* acc[0] += sum((a + add_a - b)^2): every nn.MSELoss term of loss.py:46-77 */
+int zt_mse_sum_f32(const float* a, const float* b, float add_a, int64_t n, double* acc, void* stream);
+/* Loss_inter loss.py:68-73 (LocalMean 5x5 reflect, quirk Q7): acc[0], acc[1] */
+int zt_loss_inter_f32(const float* d1, const float* d2, const float* diff, int C, int H, int W, double* acc,
+                      void* stream);
+/* Loss_Var loss.py:75-77 with calculate_local_variance utils.py:66-79: acc[0]; avg1/avg2 = C*H*W scratch */
+int zt_loss_var_f32(const float* H2, const float* H3, float* avg1, float* avg2, int C, int H, int W, double* acc,
+                    void* stream);
+
 #ifdef __cplusplus
 }
 #endif

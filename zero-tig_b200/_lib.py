@@ -50,6 +50,18 @@ SIGNATURES = {
     "zt_retinex_h2_f32": [P, P, I, P, P, L, F, P],
     "zt_retinex_h5_f32": [P, P, P, I, P, P, L, F, P],
     "zt_quantize_u8_hwc": [P, P, I, L, P],
+    "zt_bn_train_nhwc_f32": [P, I, P, I, P, I, P, P, P, P, P, I, I, F, F, P],
+    "zt_pair_downsample_f32": [P, P, P, I, I, I, F, P],
+    "zt_sub_clamp_f32": [P, F, P, I, P, I, L, F, F, I, P],
+    "zt_div_clamp_f32": [P, F, P, P, L, F, F, P],
+    "zt_texture_diff_f32": [P, P, P, I, I, P],
+    "zt_blur21_f32": [P, P, P, C.POINTER(C.c_float), I, I, I, P],
+    "zt_loss_illum_f32": [P, P, I, L, P, P, P],
+    "zt_loss_smooth_f32": [P, P, P, I, I, P, P],
+    "zt_loss_tv_f32": [P, I, I, I, P, P],
+    "zt_mse_sum_f32": [P, P, F, L, P, P],
+    "zt_loss_inter_f32": [P, P, P, I, I, I, P, P],
+    "zt_loss_var_f32": [P, P, P, P, I, I, I, P, P],
     "zt_last_error": [],
     "zt_version": [],
     "zt_launch_count": [],

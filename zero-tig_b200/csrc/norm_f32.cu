@@ -82,6 +82,52 @@ __global__ void __launch_bounds__(256) instnorm_apply_kernel(const float* __rest
   }
 }
 
+// BatchNorm2d in TRAIN mode for batch 1 (Enhancer block, model/model.py:60-67,74-81 after
+// train.py:116): batch statistics over H*W, affine, ReLU, residual add: out = res + relu(bn(x)).
+__global__ void __launch_bounds__(256) bn_train_apply_kernel(const float* __restrict__ x, int x_cs,
+                                                             float* __restrict__ out, int out_cs,
+                                                             const float* __restrict__ res, int res_cs,
+                                                             const double* __restrict__ stats,
+                                                             const float* __restrict__ gamma,
+                                                             const float* __restrict__ beta, int HW, int C, float eps,
+                                                             int64_t total4) {
+  const int c4n = C >> 2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % c4n);
+    const int64_t pix = i / c4n;
+    const double* st = stats + (int64_t)cg * 8;
+    const float4 v = __ldg(reinterpret_cast<const float4*>(x + pix * x_cs + cg * 4));
+    float r[4] = {v.x, v.y, v.z, v.w};
+    float4 rv = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (res) rv = __ldg(reinterpret_cast<const float4*>(res + pix * res_cs + cg * 4));
+    const float rr[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const double mean = st[e * 2] / HW;
+      double var = st[e * 2 + 1] / HW - mean * mean;
+      var = var < 0 ? 0 : var;
+      const float rstd = (float)(1.0 / sqrt(var + (double)eps));
+      float y = (r[e] - (float)mean) * rstd * __ldg(gamma + cg * 4 + e) + __ldg(beta + cg * 4 + e);
+      y = fmaxf(y, 0.f);
+      r[e] = res ? rr[e] + y : y;
+    }
+    *reinterpret_cast<float4*>(out + pix * out_cs + cg * 4) = make_float4(r[0], r[1], r[2], r[3]);
+  }
+}
+// running_mean / running_var update: momentum m, unbiased variance (torch BatchNorm semantics)
+__global__ void bn_update_running_kernel(const double* __restrict__ stats, float* __restrict__ rmean,
+                                         float* __restrict__ rvar, int HW, int C, float momentum) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const double mean = stats[c * 2] / HW;
+  double var = stats[c * 2 + 1] / HW - mean * mean;
+  var = var < 0 ? 0 : var;
+  const double unb = HW > 1 ? var * (double)HW / (double)(HW - 1) : var;
+  rmean[c] = (1.f - momentum) * rmean[c] + momentum * (float)mean;
+  rvar[c] = (1.f - momentum) * rvar[c] + momentum * (float)unb;
+}
+
 }  // namespace zt
 
 extern "C" int zt_instnorm_nhwc_f32(const float* x, int x_cs, float* out, int out_cs, const float* res,
@@ -103,4 +149,30 @@ extern "C" int zt_instnorm_nhwc_f32(const float* x, int x_cs, float* out, int ou
   instnorm_apply_kernel<<<blocks, 256, 0, st>>>(x, x_cs, out, out_cs, res, res_cs, stats, HW, C, eps,
                                                 relu_inner, relu_outer, total4);
   return check_launch("instnorm_apply_kernel");
+}
+
+extern "C" int zt_bn_train_nhwc_f32(const float* x, int x_cs, float* out, int out_cs, const float* res, int res_cs,
+                                    double* stats, const float* gamma, const float* beta, float* running_mean,
+                                    float* running_var, int HW, int C, float eps, float momentum, void* stream) {
+  using namespace zt;
+  ZT_REQUIRE(x && out && stats && gamma && beta, "bn_train: null pointer");
+  ZT_REQUIRE((C & 3) == 0 && C <= 1024 && (x_cs & 3) == 0 && (out_cs & 3) == 0 && (!res || (res_cs & 3) == 0),
+             "bn_train: C and strides must be multiples of 4 (C=%d)", C);
+  ZT_REQUIRE(HW > 0, "bn_train: bad dims");
+  cudaStream_t st = (cudaStream_t)stream;
+  ZT_CUDA(cudaMemsetAsync(stats, 0, sizeof(double) * 2 * C, st));
+  const int slabs = max(1, min(ceil_div(HW, 64), 4 * kNumSMs));
+  const int ppb = ceil_div(HW, slabs);
+  instnorm_stats_kernel<<<dim3(ceil_div(HW, ppb), 1), 256, 0, st>>>(x, x_cs, stats, HW, C, ppb);
+  if (int e = check_launch("instnorm_stats_kernel")) return e;
+  const int64_t total4 = (int64_t)HW * (C >> 2);
+  const int blocks = (int)std::min<int64_t>(ceil_div64(total4, 256), 8 * kNumSMs);
+  bn_train_apply_kernel<<<blocks, 256, 0, st>>>(x, x_cs, out, out_cs, res, res_cs, stats, gamma, beta, HW, C, eps,
+                                                total4);
+  if (int e = check_launch("bn_train_apply_kernel")) return e;
+  if (running_mean && running_var) {
+    bn_update_running_kernel<<<ceil_div(C, 128), 128, 0, st>>>(stats, running_mean, running_var, HW, C, momentum);
+    return check_launch("bn_update_running_kernel");
+  }
+  return ZT_OK;
 }

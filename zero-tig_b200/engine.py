@@ -389,3 +389,145 @@ class FrameEngine:
             H3_wp = s3_wp = H2
         H3, s3 = self.denoise2_H3(H3_wp, s3_wp, H2, s2, H, W)
         return dict(L2=L2, s2=s2, H2=H2, H3=H3, s3=s3, H3_wp=H3_wp, s3_wp=s3_wp)
+
+
+# ----------------------------------------------------------------------------------------
+# Training forward + losses (Network.forward / LossFunction.forward)
+# ----------------------------------------------------------------------------------------
+SMOOTH_OFFSETS = ((1, 0), (0, 1), (1, 1), (1, -1), (2, 0), (0, 2), (2, 1), (2, -1), (1, 2), (1, -2), (2, 2), (2, -2))
+LOSS_NAMES = ("enh_s2 enh_norm smooth tv res1_a res1_b res1_c res1_d res2_a res2_b res2_c res2_d "
+              "color ill inter1 inter2 var").split()
+
+
+class TrainEngine(FrameEngine):
+    """Network.forward (model/model.py:144-203) and LossFunction.forward (loss.py:23-78) on the kernels.
+    Forward values only in this round: the returned loss carries no autograd graph yet.
+    The nets run the bf16 hi/lo split here (fp32-grade): the loss gate is 1e-3 relative."""
+
+    TC_D1 = _tc_mode("TRAIN_D1", 3)
+    TC_ENH = _tc_mode("TRAIN_ENH", 3)
+    TC_D2 = _tc_mode("TRAIN_D2", 3)
+
+    def _prepare(self, device):
+        m = self.model
+        key = (str(device), _param_version(m.enhance), _param_version(m.denoise_1), _param_version(m.denoise_2))
+        fresh = key != self._wkey
+        super()._prepare(device)
+        if fresh:   # train-mode BatchNorm needs the un-folded block convolution
+            e = m.enhance
+            self.w["e.blk_raw"] = ConvW(e.conv[0].weight.to(device), e.conv[0].bias.to(device))
+
+    # L_pred = x - denoise_1(x) without clamp (model.py:149-150)
+    def denoise1_residual(self, x, H, W):
+        w, ws, HW = self.w, self.ws, H * W
+        xp, a1, a2, d = (ws.get("xp", (HW, 4)), ws.get("a48a", (HW, 48)), ws.get("a48b", (HW, 48)),
+                         ws.get("d4", (HW, 4)))
+        ops.pack_nhwc([x], 3, 0.0, xp, 4, HW)
+        ops.conv2d(w["d1.c1"], xp, 4, 4, 1, H, W, a1, 48, pad=(1, 1), act="lrelu", tc=self.TC_D1)
+        ops.conv2d(w["d1.c2"], a1, 48, 48, 1, H, W, a2, 48, pad=(1, 1), act="lrelu", tc=self.TC_D1)
+        ops.conv2d(w["d1.c3"], a2, 48, 48, 1, H, W, d, 4, tc=self.TC_D1)
+        out = torch.empty_like(x)
+        ops.sub_clamp(x, 0.0, d, 4, out, 3, HW)
+        return out
+
+    def enhance_train(self, x, H3_wp, s3_wp, L2, H, W):
+        """Enhancer.forward with BatchNorm in TRAIN mode (batch statistics, running stats updated three
+        times - model.py:60-67,74-81 under train.py:116), then H2 = clamp((x+eps)/s2, eps, 1)."""
+        w, ws, HW = self.w, self.ws, H * W
+        bn = self.model.enhance.conv[1]
+        ep, fa, fb, t = (ws.get("ep12", (HW, 12)), ws.get("f64a", (HW, 64)), ws.get("f64b", (HW, 64)),
+                         ws.get("f64t", (HW, 64)))
+        s4 = ws.get("s4", (HW, 4))
+        stats = ws.get("bn_stats", (128,), torch.float64)
+        ops.pack_nhwc([H3_wp, s3_wp, L2], 3, 0.0, ep, 12, HW)
+        ops.conv2d(w["e.in"], ep, 12, 12, 1, H, W, fa, 64, pad=(1, 1), act="relu", tc=self.TC_ENH)
+        cur, nxt = fa, fb
+        for _ in range(3):
+            ops.conv2d(w["e.blk_raw"], cur, 64, 64, 1, H, W, t, 64, pad=(1, 1), tc=self.TC_ENH)
+            ops.bn_train(t, 64, nxt, 64, cur, 64, stats, bn.weight, bn.bias, bn.running_mean, bn.running_var,
+                         HW, 64, bn.eps, bn.momentum)
+            bn.num_batches_tracked += 1
+            cur, nxt = nxt, cur
+        ops.conv2d(w["e.out"], cur, 64, 64, 1, H, W, s4, 4, pad=(1, 1), act="sigmoid", tc=self.TC_ENH)
+        s2, H2 = torch.empty_like(x), torch.empty_like(x)
+        ops.retinex_h2(x, s4, 4, s2, H2, HW, self.EPS)
+        return s2, H2
+
+    def forward_train(self, x, is_new_seq, last_H3, last_s3, of_scale, training):
+        _dev_check(x)
+        assert x.dim() == 4 and x.shape[0] == 1 and x.shape[1] == 3, "expects [1,3,H,W] (train.py uses batch 1)"
+        x = x.contiguous().float()
+        self._prepare(x.device)
+        H, W = x.shape[-2:]
+        h, wd = H // 2, W // 2
+        eps = self.EPS
+        L11, L12 = ops.pair_downsample(x, eps)
+        L_pred1 = self.denoise1_residual(L11, h, wd)
+        L_pred2 = self.denoise1_residual(L12, h, wd)
+        L2 = self.denoise1_L2(x, H, W)
+        if is_new_seq:
+            H3_wp = s3_wp = torch.zeros_like(L2)
+            H31_wp = H32_wp = s31_wp = s32_wp = torch.zeros_like(L11)
+        else:
+            H3_wp, s3_wp = self.update_cache(last_H3, last_s3, L2, of_scale)
+            H31_wp, H32_wp = ops.pair_downsample(H3_wp)
+            s31_wp, s32_wp = ops.pair_downsample(s3_wp)
+        if training:
+            s2, H2 = self.enhance_train(x, H3_wp, s3_wp, L2, H, W)
+        else:
+            s2, H2 = self.enhance_H2(x, H3_wp, s3_wp, L2, H, W)
+        s21, s22 = ops.pair_downsample(s2)
+        H11 = ops.div_clamp(L11, 0.0, s21, eps, 1.0)
+        H12 = ops.div_clamp(L12, 0.0, s22, eps, 1.0)
+        H13, s13 = self.denoise2_H3(H31_wp, s31_wp, H11, s21, h, wd)
+        H14, s14 = self.denoise2_H3(H32_wp, s32_wp, H12, s22, h, wd)
+        H3, s3 = self.denoise2_H3(H3_wp, s3_wp, H2, s2, H, W)
+        H3_pred, H4_pred = torch.cat([H13, s13], 1), torch.cat([H14, s14], 1)
+        d12 = ops.texture_diff(L_pred1, L_pred2)
+        H3d1, H3d2 = ops.pair_downsample(H3)
+        dH3 = ops.texture_diff(H3d1, H3d2)
+        H1 = ops.div_clamp(L2, 0.0, s2, 0.0, 1.0)
+        H2_blur, H3_blur = ops.blur21(H1), ops.blur21(H3)
+        self.last_wp = (H3_wp, s3_wp)
+        return (L_pred1, L_pred2, L2, s2, s21, s22, H2, H11, H12, H13, s13, H14, s14, H3, s3, H3_pred, H4_pred,
+                d12, dH3, H2_blur, H3_blur, H3d1, H3d2)
+
+    def loss_terms(self, x, outs, is_WB):
+        """The 17 weighted terms of LossFunction.forward (loss.py:46-77) as a device fp64 vector."""
+        (L_pred1, L_pred2, L2, s2, s21, s22, H2, H11, H12, H13, s13, H14, s14, H3, s3, H3_pred, H4_pred,
+         d12, dH3, H2_blur, H3_blur, H3d1, H3d2) = outs
+        x = x.contiguous().float()
+        H, W = x.shape[-2:]
+        h, wd = H // 2, W // 2
+        ws = self.ws
+        acc = torch.zeros(32, dtype=torch.float64, device=x.device)
+        chansum = ws.get("chansum", (4,), torch.float64)
+        scr1, scr2 = ws.get("loss_scr1", (1, 3, H, W)), ws.get("loss_scr2", (1, 3, H, W))
+        ops.loss_illum(L2, s2, is_WB, chansum, acc, 0)
+        ops.loss_smooth(L2, s2, scr1, acc, 2)
+        ops.loss_tv(s2, acc, 14)
+        L11, L12 = ops.pair_downsample(x, 1e-9)       # loss.py:24,51: input + 1e-9
+        den1, den2 = ops.pair_downsample(L2)
+        ops.mse_sum(L11, L_pred2, acc, 16)
+        ops.mse_sum(L12, L_pred1, acc, 17)
+        ops.mse_sum(L_pred1, den1, acc, 18)
+        ops.mse_sum(L_pred2, den2, acc, 19)
+        ops.mse_sum(H13, H12, acc, 20)
+        ops.mse_sum(s13, s22, acc, 20)
+        ops.mse_sum(H14, H11, acc, 21)
+        ops.mse_sum(s14, s21, acc, 21)
+        ops.mse_sum(H13, H3d1, acc, 22)
+        ops.mse_sum(H14, H3d2, acc, 23)
+        ops.mse_sum(H2_blur, H3_blur, acc, 24)
+        ops.mse_sum(s2, s3, acc, 25)
+        ops.loss_inter(H3d1, H3d2, dH3, acc, 26)
+        ops.loss_var(H2, H3, scr1, scr2, acc, 28)
+        n3, nh = 3.0 * H * W, 3.0 * h * wd
+        sm = sum(2.0 * acc[2 + i] / ((H - dy) * (W - abs(dx))) for i, (dy, dx) in enumerate(SMOOTH_OFFSETS))
+        tv = 2.0 * (acc[14] / ((H - 1) * W) + acc[15] / (H * (W - 1)))
+        terms = [700 * acc[0] / n3, 1000 * acc[1] / n3, 5 * sm, 1600 * tv,
+                 1000 * acc[16] / nh, 1000 * acc[17] / nh, 1000 * acc[18] / nh, 1000 * acc[19] / nh,
+                 1000 * acc[20] / (2 * nh), 1000 * acc[21] / (2 * nh), 1000 * acc[22] / nh, 1000 * acc[23] / nh,
+                 10000 * acc[24] / n3, 1000 * acc[25] / n3, 10000 * acc[26] / nh, 10000 * acc[27] / nh,
+                 1000 * acc[28] / n3]
+        return torch.stack(terms)

@@ -110,9 +110,9 @@ class Finetunemodel(nn.Module, _Recurrent):
 
 
 class Network(nn.Module, _Recurrent):
-    """Zero-shot training model (model/model.py:84-259).  Parameter tree, state handling and
-    ``update_cache`` are in place; the 23-tensor training forward / loss kernels are the next
-    scope row and raise until they land - there is deliberately no torch fallback."""
+    """Zero-shot training model (model/model.py:84-259): parameter tree, recurrent state,
+    ``update_cache``, the 23-tensor training forward and the 17 loss terms run on the CUDA kernels.
+    The backward pass is the next scope row: ``_loss`` returns the value only."""
 
     def __init__(self, args):
         super().__init__()
@@ -142,8 +142,27 @@ class Network(nn.Module, _Recurrent):
     def denoise_weights_init(self, m):
         self._init_normal(m)
 
+    def frame_engine(self):
+        from zero_tig_b200.engine import TrainEngine
+        if self._frame_engine is None:
+            self._frame_engine = TrainEngine(self)
+        return self._frame_engine
+
     def forward(self, input):
-        raise NotImplementedError("Network.forward (training) kernels are not built yet; see DESIGN.md scope table")
+        """23 tensors in the order of model/model.py:203.  BatchNorm follows ``self.training`` like the
+        reference (train.py:116 / :138); RAFT always runs in eval mode (model.py:240)."""
+        with torch.no_grad():
+            outs = self.frame_engine().forward_train(input, self.is_new_seq, self.last_H3, self.last_s3,
+                                                     self.of_scale, self.enhance.training)
+        self.last_H3_wp, self.last_s3_wp = self.frame_engine().last_wp
+        return outs
 
     def _loss(self, input):
-        raise NotImplementedError("Network._loss (training) kernels are not built yet; see DESIGN.md scope table")
+        """LossFunction.forward over Network.forward (model.py:205-215).  Forward value only in this
+        round: the scalar has no autograd graph yet (the backward kernels are the next scope row)."""
+        outs = self(input)
+        with torch.no_grad():
+            terms = self.frame_engine().loss_terms(input, outs, self.is_WB)
+        self.last_loss_terms = terms
+        self.update_H3(outs[13], outs[14])
+        return terms.sum().float()

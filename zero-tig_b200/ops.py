@@ -180,3 +180,92 @@ def retinex_h5(H2, s2, d, d_cs, H3, s3, HW, eps):
 
 def quantize_u8_hwc(x, out, Cn, HW):
     check(lib().zt_quantize_u8_hwc(_p(x), _p(out), Cn, HW, _stream()), "quantize_u8")
+
+
+# ---------------------------------------------------------------------------------------
+# training path (csrc/train.cu, csrc/norm_f32.cu)
+# ---------------------------------------------------------------------------------------
+def bn_train(x, x_cs, out, out_cs, res, res_cs, stats, gamma, beta, rmean, rvar, HW, Cn, eps, momentum):
+    check(lib().zt_bn_train_nhwc_f32(_p(x), x_cs, _p(out), out_cs, _p(res), res_cs, _p(stats), _p(gamma), _p(beta),
+                                     _p(rmean), _p(rvar), HW, Cn, eps, momentum, _stream()), "bn_train")
+
+
+def pair_downsample(x, add=0.0):
+    """utils.pair_downsampler on an NCHW [1,C,H,W] tensor (+add) -> two [1,C,H/2,W/2]."""
+    _, Cn, H, W = x.shape
+    o1 = torch.empty(1, Cn, H // 2, W // 2, device=x.device)
+    o2 = torch.empty_like(o1)
+    check(lib().zt_pair_downsample_f32(_p(x), _p(o1), _p(o2), Cn, H, W, add, _stream()), "pair_downsample")
+    return o1, o2
+
+
+def sub_clamp(a, add, d, d_cs, out, Cn, HW, lo=0.0, hi=0.0, clamp=False):
+    check(lib().zt_sub_clamp_f32(_p(a), add, _p(d), d_cs, _p(out), Cn, HW, lo, hi, int(clamp), _stream()), "sub_clamp")
+
+
+def div_clamp(a, add, b, lo, hi):
+    out = torch.empty_like(a)
+    check(lib().zt_div_clamp_f32(_p(a), add, _p(b), _p(out), a.numel(), lo, hi, _stream()), "div_clamp")
+    return out
+
+
+def texture_diff(i1, i2):
+    _, _, H, W = i1.shape
+    out = torch.empty(1, 1, H, W, device=i1.device)
+    check(lib().zt_texture_diff_f32(_p(i1), _p(i2), _p(out), H, W, _stream()), "texture_diff")
+    return out
+
+
+_BLUR_TAPS = None
+
+
+def blur_taps():
+    """1-D taps of utils.blur (utils.py:29-39 with nsig=1): sqrt(k)/sum(sqrt(k)), k = diff of the normal
+    CDF on 22 points - the reference's 2-D kernel sqrt(outer(k,k))/sum is exactly their outer product."""
+    global _BLUR_TAPS
+    if _BLUR_TAPS is None:
+        import math
+        n, nsig = 21, 1
+        interval = (2 * nsig + 1.0) / n
+        lo, hi = -nsig - interval / 2.0, nsig + interval / 2.0
+        xs = [lo + (hi - lo) * i / n for i in range(n + 1)]
+        cdf = [0.5 * (1 + math.erf(v / math.sqrt(2.0))) for v in xs]
+        r = [math.sqrt(cdf[i + 1] - cdf[i]) for i in range(n)]
+        t = sum(r)
+        _BLUR_TAPS = (C.c_float * 21)(*[v / t for v in r])
+    return _BLUR_TAPS
+
+
+def blur21(x):
+    _, Cn, H, W = x.shape
+    tmp, out = torch.empty_like(x), torch.empty_like(x)
+    check(lib().zt_blur21_f32(_p(x), _p(tmp), _p(out), blur_taps(), Cn, H, W, _stream()), "blur21")
+    return out
+
+
+def loss_illum(L2, s2, is_WB, chansum, acc, off):
+    check(lib().zt_loss_illum_f32(_p(L2), _p(s2), int(is_WB), L2.shape[2] * L2.shape[3], _p(chansum), _p(acc, off),
+                                  _stream()), "loss_illum")
+
+
+def loss_smooth(L2, s2, ycc, acc, off):
+    check(lib().zt_loss_smooth_f32(_p(L2), _p(s2), _p(ycc), L2.shape[2], L2.shape[3], _p(acc, off), _stream()),
+          "loss_smooth")
+
+
+def loss_tv(x, acc, off):
+    check(lib().zt_loss_tv_f32(_p(x), x.shape[1], x.shape[2], x.shape[3], _p(acc, off), _stream()), "loss_tv")
+
+
+def mse_sum(a, b, acc, off, add_a=0.0, n=None):
+    check(lib().zt_mse_sum_f32(_p(a), _p(b), add_a, n if n is not None else a.numel(), _p(acc, off), _stream()), "mse_sum")
+
+
+def loss_inter(d1, d2, diff, acc, off):
+    check(lib().zt_loss_inter_f32(_p(d1), _p(d2), _p(diff), d1.shape[1], d1.shape[2], d1.shape[3], _p(acc, off),
+                                  _stream()), "loss_inter")
+
+
+def loss_var(H2, H3, avg1, avg2, acc, off):
+    check(lib().zt_loss_var_f32(_p(H2), _p(H3), _p(avg1), _p(avg2), H2.shape[1], H2.shape[2], H2.shape[3],
+                                _p(acc, off), _stream()), "loss_var")
