@@ -77,6 +77,11 @@ int zt_conv2d_nhwc_f32(const ZtConv* d, void* stream);
  * in [16,256].  Same call sites as zt_conv2d_nhwc_f32. */
 int zt_conv2d_tc_nhwc(const ZtConv* d, int BN, int split, void* stream);
 
+/* Pack R rows x C fp32 (row stride rs) as the weight operand of zt_conv2d_tc_nhwc for a 1x1
+ * convolution with cout = R whose weights are produced on the device every frame: the all-pairs
+ * correlation corr.py:52-60 (weights = fmap2).  out: ceil(R/BN)*BN * ceil(C/64)*64 * 4 bytes. */
+int zt_pack_tc_rows_f32(const float* rows, int R, int C, int rs, int BN, void* out, void* stream);
+
 /* debug only: per-role timeline of CTA (0,0) of the next zt_conv2d_tc_nhwc launches; buf is a
  * device int64 array [1 + 2*cap] (zeroed by the caller), NULL disables. */
 int zt_debug_set_tc_trace(void* buf, int cap);

@@ -57,7 +57,7 @@ def test_conv_tc_matches_torch(case, split):
         assert (out[:, cout:] == 777.0).all()
 
 
-@pytest.mark.parametrize("bn", [16, 32, 64, 128, 256])
+@pytest.mark.parametrize("bn", [16, 32, 64, 128])
 def test_conv_tc_n_tiles(bn):
     from zero_tig_b200 import ops
     g = torch.Generator().manual_seed(bn)

@@ -35,6 +35,7 @@ SIGNATURES = {
     "zt_conv2d_nhwc_f32": [C.POINTER(ZtConv), P],
     "zt_conv2d_tc_nhwc": [C.POINTER(ZtConv), I, I, P],
     "zt_debug_set_tc_trace": [P, I],
+    "zt_pack_tc_rows_f32": [P, I, I, I, I, P, P],
     "zt_instnorm_nhwc_f32": [P, I, P, I, P, I, P, I, I, I, F, I, I, P],
     "zt_transpose_f32": [P, I, I, I, P, I, P],
     "zt_avgpool2_f32": [P, P, L, I, I, P],

@@ -23,6 +23,7 @@
 // model/RAFT/update.py:13-14,45-60,89-97,127-136; model/RAFT/extractor.py:46-55,167-191.
 #include <cuda_bf16.h>
 #include <stdlib.h>
+#include <algorithm>
 #include "common.cuh"
 
 namespace zt {
@@ -328,14 +329,28 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
           waited = true;
           if (lane == 0) trace(lt, 1);
         }
-        const uint32_t taddr = tmem_base + buf * (uint32_t)g.BN + ((uint32_t)(quad * 32) << 16) + (uint32_t)(ch * 32);
+        // SPLIT=3: the accumulator is [Ahi*Bhi + Alo*Bhi | Ahi*Blo] (2*BN columns); add the halves
+        const uint32_t accw = (SPLIT == 3 ? 2u : 1u) * (uint32_t)g.BN;
+        const uint32_t taddr = tmem_base + buf * accw + ((uint32_t)(quad * 32) << 16) + (uint32_t)(ch * 32);
         uint32_t v[16];
         tmem_ld16(taddr, v);
+        if (SPLIT == 3) {
+          uint32_t v2[16];
+          tmem_ld16(taddr + (uint32_t)g.BN, v2);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(v2[i]));
+        }
 #pragma unroll
         for (int i = 0; i < 4; ++i)
           *reinterpret_cast<uint4*>(stage + lane * TC_EPI_LD + 4 * i) = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
         if (ch * 32 + 16 < g.BN) {      // the second half of the chunk exists in TMEM (BN % 32 may be 16)
           tmem_ld16(taddr + 16, v);
+          if (SPLIT == 3) {
+            uint32_t v2[16];
+            tmem_ld16(taddr + 16 + (uint32_t)g.BN, v2);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(v2[i]));
+          }
 #pragma unroll
           for (int i = 0; i < 4; ++i)
             *reinterpret_cast<uint4*>(stage + lane * TC_EPI_LD + 16 + 4 * i) = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
@@ -362,10 +377,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
     {
       const uint32_t BN = g.BN, PW = g.PW, kh = d.kh, kw = d.kw;
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((BN >> 3) << 17) | (8u << 24);
+      // SPLIT=3: the hi and lo weight blocks of a stage are contiguous rows of one swizzled matrix, so
+      // Ahi * [Bhi | Blo] is ONE MMA with N = 2*BN (A is fetched once); Alo * Bhi is the second
+      const uint32_t idesc2 = (1u << 4) | (1u << 7) | (1u << 10) | ((BN >> 2) << 17) | (8u << 24);
+      const uint32_t accw = (SPLIT == 3 ? 2u : 1u) * BN;
       // descriptor templates: only the 14-bit start-address field (16 B units) changes per MMA;
       // a K step of 16 channels is +32 B inside the swizzled 128 B row
       const uint64_t descA0 = make_desc(0, PW * 128u), descB0 = make_desc(0, 1024u);
-      const uint32_t apart16 = a_part >> 4, bpart16 = b_part >> 4;
+      const uint32_t apart16 = a_part >> 4;
       const uint32_t smA16 = smem_u32(smA) >> 4, smB16 = smem_u32(smB) >> 4;
       const uint32_t a_stage16 = a_stage >> 4, b_stage16 = b_stage >> 4;
       const bool resident = g.resident != 0;
@@ -380,7 +399,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
         mbar_wait(accEmpty(buf), ((lt >> 1) & 1) ^ 1);
         tc_fence_after();
         if (lane == 0) trace(lt, 4);
-        const uint32_t tmem_d = tmem_base + buf * BN;
+        const uint32_t tmem_d = tmem_base + buf * accw;
         uint32_t acc = 0;
         int crem = cin;
         uint32_t bres16 = smB16;        // resident mode: walks the weight stages in order
@@ -410,18 +429,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
                 if (nks == 4) {
 #pragma unroll
                   for (uint32_t ks = 0; ks < 4; ++ks) {
-                    tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc, ks == 0 ? acc : 1u);
                     if (SPLIT == 3) {
+                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc2, ks == 0 ? acc : 1u);
                       tc_mma_bf16_lh(tmem_d, alo + 2 * ks + apart16, ahi, blo + 2 * ks, bhi, idesc, 1);
-                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks + bpart16, bhi, idesc, 1);
+                    } else {
+                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc, ks == 0 ? acc : 1u);
                     }
                   }
                 } else {
                   for (int ks = 0; ks < nks; ++ks) {
-                    tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc, ks == 0 ? acc : 1u);
                     if (SPLIT == 3) {
+                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc2, ks == 0 ? acc : 1u);
                       tc_mma_bf16_lh(tmem_d, alo + 2 * ks + apart16, ahi, blo + 2 * ks, bhi, idesc, 1);
-                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks + bpart16, bhi, idesc, 1);
+                    } else {
+                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc, ks == 0 ? acc : 1u);
                     }
                   }
                 }
@@ -565,6 +586,46 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
 
 }  // namespace zt
 
+namespace zt {
+// Pack R rows of C fp32 values (row-major, stride rs) as the B operand of zt_conv2d_tc_nhwc for a
+// 1x1 "convolution" whose weights change every frame (the all-pairs correlation, corr.py:52-60:
+// weights = fmap2): [n_tile][64-ch group][hi|lo][row BN][128 B swizzled], rows beyond R zero.
+__global__ void pack_tc_rows_kernel(const float* __restrict__ rows, int R, int C, int rs, int BN, int ngroups,
+                                    uint8_t* __restrict__ out, int64_t total) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int chunk_all = (int)(i % (ngroups * 8));          // 8-channel chunk index over all groups
+    const int64_t n = i / (ngroups * 8);                      // padded row index
+    const int g = chunk_all >> 3, chunk = chunk_all & 7;
+    const int nt = (int)(n / BN), r = (int)(n - (int64_t)nt * BN);
+    const int c = chunk_all * 8;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+    if (n < R && c < C) {
+      a = __ldg(reinterpret_cast<const float4*>(rows + n * rs + c));
+      b = __ldg(reinterpret_cast<const float4*>(rows + n * rs + c + 4));
+    }
+    uint2 h0, l0, h1, l1;
+    split4(a, h0, l0);
+    split4(b, h1, l1);
+    const size_t part = (size_t)BN * 128;
+    uint8_t* dst = out + ((size_t)(nt * ngroups + g) * 2) * part + (size_t)r * 128 + ((size_t)(chunk ^ (r & 7)) << 4);
+    *reinterpret_cast<uint4*>(dst) = make_uint4(h0.x, h0.y, h1.x, h1.y);
+    *reinterpret_cast<uint4*>(dst + part) = make_uint4(l0.x, l0.y, l1.x, l1.y);
+  }
+}
+}  // namespace zt
+
+extern "C" int zt_pack_tc_rows_f32(const float* rows, int R, int C, int rs, int BN, void* out, void* stream) {
+  using namespace zt;
+  ZT_REQUIRE(rows && out && R > 0 && C > 0 && (C & 7) == 0 && (rs & 3) == 0 && rs >= C, "pack_tc_rows: bad args");
+  ZT_REQUIRE(BN >= 16 && BN <= 256 && (BN & 15) == 0, "pack_tc_rows: bad BN %d", BN);
+  ZT_REQUIRE(((uintptr_t)rows & 15) == 0 && ((uintptr_t)out & 15) == 0, "pack_tc_rows: pointers must be 16-byte aligned");
+  const int ngroups = ceil_div(C, TC_CG);
+  const int64_t total = (int64_t)ceil_div(R, BN) * BN * ngroups * 8;
+  const int blocks = (int)std::min<int64_t>(ceil_div64(total, 256), 8 * kNumSMs);
+  pack_tc_rows_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(rows, R, C, rs, BN, ngroups, (uint8_t*)out, total);
+  return check_launch("pack_tc_rows_kernel");
+}
+
 static long long* g_tc_trace = nullptr;
 static int g_tc_trace_cap = 0;
 // debug: device buffer [1 + 2*cap] int64 (counter, then (tag, ns) pairs) or NULL to disable
@@ -608,7 +669,8 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
   g.trace = g_tc_trace;
   g.trace_cap = g_tc_trace_cap;
   g.tmem_cols = 32;
-  while (g.tmem_cols < 2 * BN) g.tmem_cols <<= 1;
+  ZT_REQUIRE(split == 1 || BN <= 128, "conv_tc: the hi/lo split keeps 2*BN accumulator columns, BN=%d > 128", BN);
+  while (g.tmem_cols < (split == 3 ? 4 : 2) * BN) g.tmem_cols <<= 1;
   const int npart = split == 3 ? 2 : 1;
   const size_t a_stage = (size_t)g.a_part * npart;
   const size_t b_stage = (size_t)BN * 128 * npart;

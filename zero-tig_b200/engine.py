@@ -52,6 +52,7 @@ class RaftEngine:
     TC_ENC = _tc_mode("RAFT_ENC", TC)      # fnet / cnet
     TC_UPD = _tc_mode("RAFT_UPD", TC)      # motion encoder + GRU
     TC_HEAD = _tc_mode("RAFT_HEAD", TC)    # flow head + mask head
+    TC_CORR = _tc_mode("RAFT_CORR", 3 if TC else 0)   # all-pairs correlation volume
 
     def __init__(self, raft):
         self.raft = raft
@@ -162,9 +163,6 @@ class RaftEngine:
         fmap = ws.get("fmap", (2 * N, 256))
         ops.conv2d(w["fnet.conv2"], f, 128, 128, 2, h8, w8, fmap, 256, tc=T, bn=64)
         # all-pairs correlation volume + pyramid (corr.py:13-27,52-60)
-        N4 = (N + 3) // 4 * 4
-        f2t = ws.get("f2t", (256, N4))
-        ops.transpose(fmap[N:], N, 256, 256, f2t, N4)
         hs, wsz = [h8], [w8]
         for _ in range(3):
             hs.append(hs[-1] // 2)
@@ -173,9 +171,22 @@ class RaftEngine:
             raise RuntimeError("RAFT grid %dx%d is too small: the reference's 4-level lookup yields NaN when the "
                                "coarsest level is below 2x2 (needs a feature grid >= 16x16)" % (h8, w8))
         lv = [ws.get(f"corr{i}", (N, hs[i] * wsz[i])) for i in range(4)]
-        cw = ConvW.__new__(ConvW)
-        cw.w, cw.b, cw.kh, cw.kw, cw.cin, cw.cout, cw.w_cs = f2t, None, 1, 1, 256, N, N4
-        ops.conv2d(cw, fmap, 256, 256, 1, h8, w8, lv[0], N, scale=0.0625)
+        if self.TC_CORR:
+            # fmap1 x fmap2^T / sqrt(256) on the tensor cores (hi/lo split): fmap2 is packed as the
+            # "weights" of a 1x1 convolution with cout = N
+            cw = ws.bufs.get(("corr_w", N))
+            if cw is None:
+                cw = ops.RowsAsWeights(N, 256, 128, x2.device)
+                ws.bufs[("corr_w", N)] = cw
+            cw.pack(fmap[N:], 256)
+            ops.conv2d(cw, fmap, 256, 256, 1, h8, w8, lv[0], N, scale=0.0625, tc=self.TC_CORR, bn=128)
+        else:
+            N4 = (N + 3) // 4 * 4
+            f2t = ws.get("f2t", (256, N4))
+            ops.transpose(fmap[N:], N, 256, 256, f2t, N4)
+            cw = ConvW.__new__(ConvW)
+            cw.w, cw.b, cw.kh, cw.kw, cw.cin, cw.cout, cw.w_cs = f2t, None, 1, 1, 256, N, N4
+            ops.conv2d(cw, fmap, 256, 256, 1, h8, w8, lv[0], N, scale=0.0625)
         for i in range(3):
             ops.avgpool2(lv[i], lv[i + 1], N, hs[i], wsz[i])
         # context network

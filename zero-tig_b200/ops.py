@@ -108,6 +108,26 @@ def conv2d(wt: ConvW, in0, in0_cs, c0, B, H, W, out, out_cs, *, in0_off=0, in1=N
     return Ho, Wo
 
 
+class RowsAsWeights:
+    """Device rows [R][C] used as the weights of a 1x1 tensor-core convolution with cout = R (the
+    all-pairs correlation corr.py:52-60: weights = fmap2, re-packed on the device every frame)."""
+
+    def __init__(self, R, Cn, BN, device):
+        self.kh = self.kw = 1
+        self.cin, self.cout, self.b, self.BN = Cn, R, None, BN
+        self.w, self.w_cs = None, 0
+        nt, ng = (R + BN - 1) // BN, (Cn + 63) // 64
+        self.buf = torch.empty(nt * ng * 2 * BN * 128, dtype=torch.uint8, device=device)
+
+    def pack(self, rows, rs):
+        check(lib().zt_pack_tc_rows_f32(_p(rows), self.cout, self.cin, rs, self.BN, _p(self.buf), _stream()),
+              "pack_tc_rows")
+
+    def tc_pack(self, BN):
+        assert BN == self.BN
+        return self.buf
+
+
 def instnorm(x, x_cs, out, out_cs, stats, B, HW, Cn, relu_inner, relu_outer=False, res=None, res_cs=0, eps=1e-5):
     check(lib().zt_instnorm_nhwc_f32(_p(x), x_cs, _p(out), out_cs, _p(res), res_cs, _p(stats), B, HW, Cn,
                                      eps, int(relu_inner), int(relu_outer), _stream()), "instnorm")
