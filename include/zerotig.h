@@ -190,6 +190,58 @@ int zt_loss_inter_f32(const float* d1, const float* d2, const float* diff, int C
 int zt_loss_var_f32(const float* H2, const float* H3, float* avg1, float* avg2, int C, int H, int W, double* acc,
                     void* stream);
 
+/* ---- training backward (train.py:126-131): adjoints of the loss terms, of the Retinex glue and of
+ * the networks.  Frame-level gradients are NCHW fp32 planes the entry points ACCUMULATE into (the
+ * host zeroes them once per step); network-internal gradients are NHWC like the activations.  The
+ * data gradient of a convolution is the forward convolution (zt_conv2d_tc_nhwc) with spatially
+ * flipped, transposed weights. */
+/* nn.MSELoss backward: d = coef*((a+add_a)-b); ga += d (if non-null); gb -= d (if non-null) */
+int zt_mse_bwd_f32(const float* a, const float* b, float add_a, int64_t n, float coef, float* ga, float* gb,
+                   void* stream);
+/* loss.py:40-47 adjoint w.r.t. s2: g_s2 += c0*(s2-bright) + c1*(norm_ll-adj)*d norm_ll/d s2 */
+int zt_loss_illum_bwd_f32(const float* L2, const float* s2, int is_WB, int64_t HW, const double* chansum, float c0,
+                          float c1, float* g_s2, void* stream);
+/* SmoothLoss loss.py:193-311 adjoint w.r.t. the illumination map; coef = 12 HOST floats (weight*2/count) */
+int zt_loss_smooth_bwd_f32(const float* ycc, const float* s2, int H, int W, const float* coef, float* g_s2,
+                           void* stream);
+/* L_TV loss.py:139-152 adjoint: ch, cw = weight*2/count of the vertical / horizontal sums */
+int zt_loss_tv_bwd_f32(const float* x, int C, int H, int W, float ch, float cw, float* g, void* stream);
+/* Loss_inter loss.py:66-73 adjoint incl. LocalMean^T (reflect 5x5); u1,u2 = C*H*W scratch */
+int zt_loss_inter_bwd_f32(const float* d1, const float* d2, const float* diff, int C, int H, int W, float coef,
+                          float* u1, float* u2, float* g_d1, float* g_d2, void* stream);
+/* Loss_Var loss.py:75-77 adjoint through calculate_local_variance (utils.py:66-79); t0..t2 scratch */
+int zt_loss_var_bwd_f32(const float* H2, const float* H3, const float* avg1, const float* avg2, int C, int H, int W,
+                        float coef, float* t0, float* t1, float* t2, float* g_H2, float* g_H3, void* stream);
+/* utils.blur adjoint (reflect-pad folding included): g_out += blur^T(g_in) */
+int zt_blur21_bwd_f32(const float* g_in, float* tmp, float* g_out, const float* taps, int C, int H, int W,
+                      void* stream);
+/* pair_downsampler^T (utils.py:15-24): gx += scatter of g1 (anti-diagonal) and g2 (diagonal) */
+int zt_pair_downsample_bwd_f32(const float* g1, const float* g2, int C, int H, int W, float* gx, void* stream);
+/* clamp((a+add)/b, lo, hi) adjoint w.r.t. b (model.py:170-177) */
+int zt_div_clamp_bwd_f32(const float* a, float add, const float* b, const float* g_out, int64_t n, float lo, float hi,
+                         float* g_b, void* stream);
+/* NHWC gradient of a network output from one or two NCHW gradient planes, sign applied and masked by the
+ * clamp of the matching forward output (model.py:152,180-191; o* may be null = no clamp) */
+int zt_mask_pack_nhwc_f32(const float* g0, const float* o0, const float* g1, const float* o1, int c_each, int nsrc,
+                          float sign, float lo, float hi, float* out, int cs, int64_t HW, void* stream);
+/* d_k[c][p] += g[p][c_off + k*c_each + c]: gradient of the non-detached torch.cat inputs of denoise_2 */
+int zt_unpack_add_nchw_f32(const float* g, int cs, int c_off, int c_each, int nd, float* d0, float* d1, int64_t HW,
+                           void* stream);
+/* g *= act'(y) with the derivative written through the activation output y (ZT_ACT_*) */
+int zt_act_bwd_nhwc_f32(float* g, int g_cs, const float* y, int y_cs, int C, int act, int64_t M, void* stream);
+/* backward of zt_bn_train_nhwc_f32 (BatchNorm2d train mode + ReLU; the residual passes dout through) */
+int zt_bn_train_bwd_nhwc_f32(const float* x, int x_cs, const float* dout, int d_cs, const double* stats, double* red,
+                             const float* gamma, const float* beta, int HW, int C, float eps, float* dx, int dx_cs,
+                             float* dgamma, float* dbeta, void* stream);
+/* nn.Conv2d weight / bias gradient, stride 1: dW[kh][kw][cin][w_cs] += X^T * G per tap; dbias += colsum(G) */
+int zt_conv2d_wgrad_nhwc_f32(const float* X, int x_cs, const float* G, int g_cs, float* dW, float* dbias, int H, int W,
+                             int kh, int kw, int ph, int pw, int cin, int cout, int w_cs, void* stream);
+/* clip_grad_norm_ + torch.optim.Adam step (train.py:98,130-131) over flat fp32 buffers, optional
+ * pre-scale of the gradients (1/world after the NCCL all-reduce) */
+int zt_clip_adam_f32(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, double* sumsq,
+                     float grad_scale, float max_norm, float lr, float beta1, float beta2, float eps,
+                     float weight_decay, int step, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

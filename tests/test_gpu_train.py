@@ -98,3 +98,266 @@ def test_training_kernels_vs_oracle():
     ops.loss_tv(x.cuda(), acc, 0)
     tv = 2.0 * (acc[0] / (45 * 58) + acc[1] / (46 * 57))
     assert abs(tv.item() - O.tv_loss(x).item()) < 1e-5 * O.tv_loss(x).item()
+
+
+# ------------------------------------------------------------------------------------------
+# backward pass (train.py:126-131)
+# ------------------------------------------------------------------------------------------
+def _rel(a, b):
+    a, b = a.double().cpu(), b.double().cpu()
+    return ((a - b).norm() / (b.norm() + 1e-30)).item()
+
+
+# The enhancer trunk (in_conv / shared block / BatchNorm) sits behind three train-mode BatchNorm
+# backward passes whose mean subtractions cancel most of the incoming gradient: the reference's own fp32
+# CPU run and the fp32 CPU oracle already differ by 5e-4 there (1e-7 elsewhere).  Those tensors are gated
+# at 1e-2, everything else at the 1e-3 of SURVEY 8d.
+_TRUNK = ("enhance.in_conv.0.weight", "enhance.in_conv.0.bias", "enhance.conv.0.weight", "enhance.conv.1.weight",
+          "enhance.conv.1.bias")
+
+
+@pytest.mark.parametrize("tag", ["rlv", "uw"])
+def test_loss_backward_vs_reference_golden(tag, weights):
+    """loss.backward() through Network._loss fills .grad of the 20 trainable tensors; compared with the
+    gradients of the unmodified reference on frame 1 of the golden clip (RAFT + warp in the loop)."""
+    from zero_tig_b200 import synth
+    from zero_tig_b200.engine import TRAIN_PARAMS
+    from zero_tig_b200.model.model import Network
+    g = np.load(os.path.join(GOLDEN, f"train_{tag}.npz"))
+    H, W, of_scale, n, stride = [int(v) for v in g["meta"]]
+    net = Network(synth.make_args(dataset="underwater" if tag == "uw" else "RLV", of_scale=of_scale)).cuda()
+    net.load_state_dict(weights)
+    net.train()
+    clip = synth.synthetic_clip(n, H, W, seed=3, underwater=(tag == "uw"))
+    for t in range(n):
+        x = clip[t:t + 1].cuda()
+        net.is_new_seq = (t == 0)
+        net(x)
+        net.load_state_dict(weights)
+        net.zero_grad()
+        loss = net._loss(x)
+        assert loss.requires_grad and loss.grad_fn is not None
+        loss.backward()
+        net.load_state_dict(weights)
+    named = dict(net.named_parameters())
+    assert all(p.grad is None for k, p in named.items() if k.startswith("raft."))
+    wscale = torch.from_numpy(g["grad.enhance.conv.0.weight"]).norm().item()
+    for k in TRAIN_PARAMS:
+        ref = torch.from_numpy(g["grad." + k])
+        got = named[k].grad
+        assert got is not None and got.shape == ref.shape, k
+        if k == "enhance.conv.0.bias":   # a bias in front of BatchNorm: the true gradient is zero (rounding noise)
+            assert (got.cpu() - ref).norm().item() <= 1e-4 * wscale, k
+            continue
+        assert _rel(got, ref) <= (1e-2 if k in _TRUNK else 1e-3), (k, _rel(got, ref))
+
+
+def test_backward_kernels_vs_autograd():
+    """Every adjoint kernel against torch autograd over the oracle restatement (odd sizes, borders)."""
+    import torch.nn.functional as F
+    import zt_oracle as O
+    from zero_tig_b200 import ops
+    g = torch.Generator().manual_seed(11)
+    H, W = 38, 50
+    x = torch.rand(1, 3, H, W, generator=g)
+    y = torch.rand(1, 3, H, W, generator=g)
+    go = torch.randn(1, 3, H, W, generator=g)
+
+    def grad_of(fn, *ins):
+        ins = [i.clone().requires_grad_(True) for i in ins]
+        return torch.autograd.grad(fn(*ins), ins, allow_unused=True)
+
+    # blur^T (reflect folding at the borders)
+    ref, = grad_of(lambda a: (O.blur(a) * go).sum(), x)
+    out = torch.zeros_like(x).cuda()
+    ops.blur21_bwd(go.cuda(), torch.empty_like(out), out)
+    assert _rel(out, ref) < 1e-5
+    # pair_downsampler^T
+    g1, g2 = torch.randn(1, 3, H // 2, W // 2, generator=g), torch.randn(1, 3, H // 2, W // 2, generator=g)
+    ref, = grad_of(lambda a: sum((o * gg).sum() for o, gg in zip(O.pair_downsampler(a), (g1, g2))), x)
+    out = torch.zeros_like(x).cuda()
+    ops.pair_downsample_bwd(g1.cuda(), g2.cuda(), out)
+    assert _rel(out, ref) < 1e-6
+    # TV
+    ref, = grad_of(lambda a: 1600 * O.tv_loss(a), x)
+    out = torch.zeros_like(x).cuda()
+    ops.loss_tv_bwd(x.cuda(), 1600 * 2.0 / ((H - 1) * W), 1600 * 2.0 / (H * (W - 1)), out)
+    assert _rel(out, ref) < 1e-5
+    # SmoothLoss w.r.t. the illumination map
+    s = 0.2 + 0.6 * torch.rand(1, 3, H, W, generator=g)
+    ref = grad_of(lambda a, b: 5 * O.smooth_loss(a, b), x, s)[1]
+    from zero_tig_b200.engine import SMOOTH_OFFSETS
+    ycc, acc = torch.empty_like(x).cuda(), torch.zeros(12, dtype=torch.float64, device="cuda")
+    ops.loss_smooth(x.cuda(), s.cuda(), ycc, acc, 0)
+    out = torch.zeros_like(x).cuda()
+    ops.loss_smooth_bwd(ycc, s.cuda(), [5 * 2.0 / ((H - dy) * (W - abs(dx))) for dy, dx in SMOOTH_OFFSETS], out)
+    assert _rel(out, ref) < 1e-4
+    # illumination targets (RLV and white-balance variants)
+    L2 = 0.02 + 0.2 * torch.rand(1, 3, H, W, generator=g)
+    for is_WB in (False, True):
+        n3 = 3.0 * H * W
+        eps = 1e-9
+        def illum(b):
+            L2d = L2
+            if is_WB:
+                ef = (0.3 / (L2d.mean(dim=(2, 3)) + eps)).unsqueeze(2).unsqueeze(3)
+            else:
+                Y = L2d[:, 2] * 0.299 + L2d[:, 1] * 0.587 + L2d[:, 0] * 0.144
+                ef = (0.5 / (Y.mean(dim=(1, 2)) + eps)).view(-1, 1, 1, 1).repeat(1, 3, 1, 1)
+            ef = torch.clamp(ef, 1, 25)
+            ratio = torch.pow(torch.tensor(0.7), -ef) / ef
+            nl = torch.clamp(L2d / b, eps, 0.8)
+            bright = torch.clamp(torch.pow(L2d * ef, ef) * ratio, eps, 1)
+            adj = torch.clamp(L2d * ef, eps, 1)
+            return 700 * F.mse_loss(b, bright) + 1000 * F.mse_loss(nl, adj)
+        ref, = grad_of(illum, s)
+        chansum, acc = torch.zeros(4, dtype=torch.float64, device="cuda"), torch.zeros(2, dtype=torch.float64, device="cuda")
+        ops.loss_illum(L2.cuda(), s.cuda(), is_WB, chansum, acc, 0)
+        out = torch.zeros_like(x).cuda()
+        ops.loss_illum_bwd(L2.cuda(), s.cuda(), is_WB, chansum, 700 * 2 / n3, 1000 * 2 / n3, out)
+        assert _rel(out, ref) < 1e-4, is_WB
+    # Loss_inter (LocalMean^T, quirk Q7)
+    D = (torch.rand(1, 1, H, W, generator=g) > 0.6).float()
+
+    def inter(a, b):
+        lm1, lm2 = O._box5_reflect(a), O._box5_reflect(b)
+        return 10000 * (F.mse_loss(a, (1 - D) * lm1 + a * D) + F.mse_loss(b, (1 - D) * lm2 + a * D))
+    r1, r2 = grad_of(inter, x, y)
+    o1, o2 = torch.zeros_like(x).cuda(), torch.zeros_like(x).cuda()
+    ops.loss_inter_bwd(x.cuda(), y.cuda(), D.cuda(), 10000 * 2 / (3.0 * H * W), torch.empty_like(o1), torch.empty_like(o1),
+                       o1, o2)
+    assert _rel(o1, r1) < 1e-5 and _rel(o2, r2) < 1e-5
+    # Loss_Var through calculate_local_variance
+    r1, r2 = grad_of(lambda a, b: 1000 * F.mse_loss(O.local_variance(a), O.local_variance(b - a)), x, y)
+    a1, a2 = torch.empty_like(x).cuda(), torch.empty_like(x).cuda()
+    acc = torch.zeros(1, dtype=torch.float64, device="cuda")
+    ops.loss_var(x.cuda(), y.cuda(), a1, a2, acc, 0)
+    o1, o2 = torch.zeros_like(x).cuda(), torch.zeros_like(x).cuda()
+    t = [torch.empty_like(o1) for _ in range(3)]
+    ops.loss_var_bwd(x.cuda(), y.cuda(), a1, a2, 1000 * 2 / (3.0 * H * W), t[0], t[1], t[2], o1, o2)
+    assert _rel(o1, r1) < 1e-4 and _rel(o2, r2) < 1e-4
+    # clamp(a / b) w.r.t. b
+    ref = grad_of(lambda a, b: (torch.clamp((a + 1e-4) / b, 1e-4, 1) * go).sum(), x, s)[1]
+    out = torch.zeros_like(x).cuda()
+    ops.div_clamp_bwd(x.cuda(), 1e-4, s.cuda(), go.cuda(), 1e-4, 1.0, out)
+    assert _rel(out, ref) < 1e-5
+
+
+@pytest.mark.parametrize("cin,cout,k,H,W", [(64, 64, 3, 33, 70), (48, 48, 3, 20, 129), (12, 48, 3, 17, 64),
+                                             (4, 48, 3, 9, 31), (64, 3, 3, 21, 40), (48, 6, 1, 16, 65),
+                                             (48, 3, 1, 8, 8)])
+def test_conv_wgrad_dgrad_vs_torch(cin, cout, k, H, W):
+    """zt_conv2d_wgrad_nhwc_f32 and the flipped-weight data gradient against torch autograd."""
+    import torch.nn.functional as F
+    from zero_tig_b200 import ops
+    g = torch.Generator().manual_seed(cin * 100 + cout)
+    x = torch.randn(1, cin, H, W, generator=g).requires_grad_(True)
+    w = (torch.randn(cout, cin, k, k, generator=g) * 0.1).requires_grad_(True)
+    b = torch.randn(cout, generator=g).requires_grad_(True)
+    go = torch.randn(1, cout, H, W, generator=g)
+    (F.conv2d(x, w, b, padding=k // 2) * go).sum().backward()
+    cin_p, co_p = (cin + 3) // 4 * 4, (cout + 3) // 4 * 4
+    xn = torch.zeros(H * W, cin_p).cuda()
+    xn[:, :cin] = x.detach()[0].permute(1, 2, 0).reshape(H * W, cin)
+    gn = torch.zeros(H * W, co_p).cuda()
+    gn[:, :cout] = go[0].permute(1, 2, 0).reshape(H * W, cout)
+    fw = ops.ConvW(w.detach().cuda(), b.detach().cuda(), cin_pad=cin_p)
+    wg = ops.WGrad(fw, w.shape, "cuda")
+    wg.accumulate(xn, cin_p, gn, co_p, H, W, (k // 2, k // 2))
+    wg.accumulate(xn, cin_p, gn, co_p, H, W, (k // 2, k // 2))     # accumulates
+    dw, db = wg.grads()
+    assert _rel(dw, 2 * w.grad) < 1e-5 and _rel(db, 2 * b.grad) < 1e-5
+    bw = ops.dgrad_weights(w.detach().cuda(), cin_pad=co_p)
+    dx = torch.empty(H * W, cin_p).cuda()
+    ops.conv2d(bw, gn, co_p, co_p, 1, H, W, dx, cin_p, pad=(k // 2, k // 2), tc=3)
+    ref = x.grad[0].permute(1, 2, 0).reshape(H * W, cin)
+    assert _rel(dx[:, :cin], ref) < 1e-4
+
+
+def test_bn_train_backward_vs_torch():
+    from zero_tig_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    HW, Cn = 37 * 41, 64
+    x = torch.randn(1, Cn, 37, 41, generator=g).requires_grad_(True)
+    res = torch.randn(1, Cn, 37, 41, generator=g)
+    bn = torch.nn.BatchNorm2d(Cn)
+    with torch.no_grad():
+        bn.weight.normal_(1.0, 0.2, generator=g)
+        bn.bias.normal_(0.0, 0.2, generator=g)
+    go = torch.randn(1, Cn, 37, 41, generator=g)
+    ((res + torch.relu(bn(x))) * go).sum().backward()
+    nhwc = lambda t: t.detach()[0].permute(1, 2, 0).reshape(HW, Cn).contiguous().cuda()
+    stats = torch.zeros(2 * Cn, dtype=torch.float64, device="cuda")
+    out = torch.empty(HW, Cn).cuda()
+    gm, bt = bn.weight.detach().cuda(), bn.bias.detach().cuda()
+    ops.bn_train(nhwc(x), Cn, out, Cn, nhwc(res), Cn, stats, gm, bt, None, None, HW, Cn, bn.eps, 0.1)
+    dx, dgb = torch.empty(HW, Cn).cuda(), torch.zeros(2, Cn).cuda()
+    red = torch.zeros(2 * Cn, dtype=torch.float64, device="cuda")
+    ops.bn_train_bwd(nhwc(x), Cn, nhwc(go), Cn, stats, red, gm, bt, HW, Cn, bn.eps, dx, Cn, dgb[0], dgb[1])
+    assert _rel(dx, nhwc(x.grad)) < 1e-4
+    assert _rel(dgb[0], bn.weight.grad) < 1e-5 and _rel(dgb[1], bn.bias.grad) < 1e-5
+
+
+def test_clip_adam_vs_torch(weights):
+    """ClipAdam (flat buffers, fused clip + Adam kernel) against clip_grad_norm_ + torch.optim.Adam."""
+    from zero_tig_b200.optim import ClipAdam
+    g = torch.Generator().manual_seed(9)
+    shapes = [(64, 9, 3, 3), (64,), (48, 48, 3, 3), (3,)]
+    ref = [torch.nn.Parameter((torch.randn(s, generator=g) * 0.05).cuda()) for s in shapes]
+    mine = [torch.nn.Parameter(p.detach().clone()) for p in ref]
+    opt_ref = torch.optim.Adam(ref, lr=1e-4, betas=(0.9, 0.999), weight_decay=3e-4)
+    opt = ClipAdam(mine, lr=1e-4, betas=(0.9, 0.999), weight_decay=3e-4, max_norm=5.0)
+    for it in range(5):
+        grads = [(torch.randn(s, generator=g) * (3.0 if it % 2 else 0.01)).cuda() for s in shapes]
+        for p, q, gr in zip(ref, mine, grads):
+            p.grad = gr.clone()
+            if it < 3:
+                q.grad.copy_(gr)        # in place into the flat views
+            else:
+                q.grad = gr.clone()     # replaced tensors are gathered by step()
+        torch.nn.utils.clip_grad_norm_(ref, 5.0)
+        opt_ref.step()
+        opt.step()
+        for p, q in zip(ref, mine):
+            assert (p - q).abs().max().item() < 2e-7, it
+    assert all(q.data_ptr() >= opt.flat.data_ptr() for q in mine)
+
+
+def test_training_step_decreases_loss(weights):
+    """A few full steps (forward, CUDA backward, fused clip+Adam) on one frame: the loss goes down and the
+    torch-side optimiser path of train.py:126-131 gives the same first update."""
+    from zero_tig_b200 import synth
+    from zero_tig_b200.model.model import Network
+    from zero_tig_b200.optim import ClipAdam
+    x = synth.synthetic_clip(1, 96, 128, seed=5).cuda()
+    nets = []
+    for _ in range(2):
+        net = Network(synth.make_args(of_scale=1)).cuda()
+        net.load_state_dict(weights)
+        net.train()
+        nets.append(net)
+    a, b = nets
+    opt_a = ClipAdam(a.trainable(), lr=1e-4, weight_decay=3e-4, max_norm=5.0)
+    opt_b = torch.optim.Adam(b.parameters(), lr=1e-4, betas=(0.9, 0.999), weight_decay=3e-4)
+    losses = []
+    for it in range(4):
+        a.is_new_seq = True
+        opt_a.zero_grad()
+        la = a._loss(x)
+        la.backward()
+        opt_a.step()
+        losses.append(la.item())
+        if it == 0:
+            b.is_new_seq = True
+            opt_b.zero_grad()
+            lb = b._loss(x)
+            lb.backward()
+            torch.nn.utils.clip_grad_norm_(b.parameters(), 5)
+            opt_b.step()
+            assert abs(la.item() - lb.item()) < 1e-6 * abs(lb.item())
+            from zero_tig_b200.engine import TRAIN_PARAMS
+            for k, p, q in zip(TRAIN_PARAMS, a.trainable(), b.trainable()):
+                if k == "enhance.conv.0.bias":
+                    continue   # zero true gradient (bias before BatchNorm): Adam turns rounding noise into +-lr
+                assert (p - q).abs().max().item() < 1e-6, k
+    assert losses[-1] < losses[0], losses

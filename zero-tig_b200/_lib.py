@@ -63,6 +63,21 @@ SIGNATURES = {
     "zt_mse_sum_f32": [P, P, F, L, P, P],
     "zt_loss_inter_f32": [P, P, P, I, I, I, P, P],
     "zt_loss_var_f32": [P, P, P, P, I, I, I, P, P],
+    "zt_mse_bwd_f32": [P, P, F, L, F, P, P, P],
+    "zt_loss_illum_bwd_f32": [P, P, I, L, P, F, F, P, P],
+    "zt_loss_smooth_bwd_f32": [P, P, I, I, C.POINTER(C.c_float), P, P],
+    "zt_loss_tv_bwd_f32": [P, I, I, I, F, F, P, P],
+    "zt_loss_inter_bwd_f32": [P, P, P, I, I, I, F, P, P, P, P, P],
+    "zt_loss_var_bwd_f32": [P, P, P, P, I, I, I, F, P, P, P, P, P, P],
+    "zt_blur21_bwd_f32": [P, P, P, C.POINTER(C.c_float), I, I, I, P],
+    "zt_pair_downsample_bwd_f32": [P, P, I, I, I, P, P],
+    "zt_div_clamp_bwd_f32": [P, F, P, P, L, F, F, P, P],
+    "zt_mask_pack_nhwc_f32": [P, P, P, P, I, I, F, F, F, P, I, L, P],
+    "zt_unpack_add_nchw_f32": [P, I, I, I, I, P, P, L, P],
+    "zt_act_bwd_nhwc_f32": [P, I, P, I, I, I, L, P],
+    "zt_bn_train_bwd_nhwc_f32": [P, I, P, I, P, P, P, P, I, I, F, P, I, P, P, P],
+    "zt_conv2d_wgrad_nhwc_f32": [P, I, P, I, P, P, I, I, I, I, I, I, I, I, I, P],
+    "zt_clip_adam_f32": [P, P, P, P, L, P, F, F, F, F, F, F, F, I, P],
     "zt_last_error": [],
     "zt_version": [],
     "zt_launch_count": [],

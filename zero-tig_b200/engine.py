@@ -300,13 +300,14 @@ class FrameEngine:
             self.ws = _Workspace(device)
 
     # ---- nets ----
-    def denoise1_L2(self, x, H, W):
-        """L2 = clamp((x+eps) - denoise_1(x+eps), eps, 1)   (model.py:313-316)."""
+    def denoise1_L2(self, x, H, W, tag=""):
+        """L2 = clamp((x+eps) - denoise_1(x+eps), eps, 1)   (model.py:313-316).  `tag` names a private set of
+        activation buffers (training keeps them for the backward pass)."""
         w, ws, HW = self.w, self.ws, H * W
-        xp = ws.get("xp", (HW, 4))
-        a1 = ws.get("a48a", (HW, 48))
-        a2 = ws.get("a48b", (HW, 48))
-        d = ws.get("d4", (HW, 4))
+        xp = ws.get("xp" + tag, (HW, 4))
+        a1 = ws.get("a48a" + tag, (HW, 48))
+        a2 = ws.get("a48b" + tag, (HW, 48))
+        d = ws.get("d4" + tag, (HW, 4))
         ops.pack_nhwc([x], 3, self.EPS, xp, 4, HW)
         ops.conv2d(w["d1.c1"], xp, 4, 4, 1, H, W, a1, 48, pad=(1, 1), act="lrelu", tc=self.TC_D1)
         ops.conv2d(w["d1.c2"], a1, 48, 48, 1, H, W, a2, 48, pad=(1, 1), act="lrelu", tc=self.TC_D1)
@@ -335,13 +336,13 @@ class FrameEngine:
         ops.retinex_h2(x, s4, 4, s2, H2, HW, self.EPS)
         return s2, H2
 
-    def denoise2_H3(self, H3_wp, s3_wp, H2, s2, H, W):
+    def denoise2_H3(self, H3_wp, s3_wp, H2, s2, H, W, tag=""):
         """H5 = clamp(cat[H2,s2] - denoise_2(cat[H3_wp,s3_wp,H2,s2]), eps, 1)  (model.py:334-337)."""
         w, ws, HW = self.w, self.ws, H * W
-        dp = ws.get("dp12", (HW, 12))
-        a1 = ws.get("a48a", (HW, 48))
-        a2 = ws.get("a48b", (HW, 48))
-        d = ws.get("d8", (HW, 8))
+        dp = ws.get("dp12" + tag, (HW, 12))
+        a1 = ws.get("a48a" + tag, (HW, 48))
+        a2 = ws.get("a48b" + tag, (HW, 48))
+        d = ws.get("d8" + tag, (HW, 8))
         ops.pack_nhwc([H3_wp, s3_wp, H2, s2], 3, 0.0, dp, 12, HW)
         ops.conv2d(w["d2.c1"], dp, 12, 12, 1, H, W, a1, 48, pad=(1, 1), act="lrelu", tc=self.TC_D2)
         ops.conv2d(w["d2.c2"], a1, 48, 48, 1, H, W, a2, 48, pad=(1, 1), act="lrelu", tc=self.TC_D2)
@@ -403,21 +404,28 @@ class FrameEngine:
 
 
 # ----------------------------------------------------------------------------------------
-# Training forward + losses (Network.forward / LossFunction.forward)
+# Training step: Network.forward / LossFunction.forward and their backward pass
 # ----------------------------------------------------------------------------------------
 SMOOTH_OFFSETS = ((1, 0), (0, 1), (1, 1), (1, -1), (2, 0), (0, 2), (2, 1), (2, -1), (1, 2), (1, -2), (2, 2), (2, -2))
 LOSS_NAMES = ("enh_s2 enh_norm smooth tv res1_a res1_b res1_c res1_d res2_a res2_b res2_c res2_d "
               "color ill inter1 inter2 var").split()
+# trainable parameters in the order the gradients are returned (== Network.named_parameters() minus raft.*)
+TRAIN_PARAMS = ("enhance.in_conv.0.weight enhance.in_conv.0.bias enhance.conv.0.weight enhance.conv.0.bias "
+                "enhance.conv.1.weight enhance.conv.1.bias enhance.out_conv.0.weight enhance.out_conv.0.bias "
+                "denoise_1.conv1.weight denoise_1.conv1.bias denoise_1.conv2.weight denoise_1.conv2.bias "
+                "denoise_1.conv3.weight denoise_1.conv3.bias denoise_2.conv1.weight denoise_2.conv1.bias "
+                "denoise_2.conv2.weight denoise_2.conv2.bias denoise_2.conv3.weight denoise_2.conv3.bias").split()
 
 
 class TrainEngine(FrameEngine):
-    """Network.forward (model/model.py:144-203) and LossFunction.forward (loss.py:23-78) on the kernels.
-    Forward values only in this round: the returned loss carries no autograd graph yet.
-    The nets run the bf16 hi/lo split here (fp32-grade): the loss gate is 1e-3 relative."""
+    """Network.forward (model/model.py:144-203), LossFunction.forward (loss.py:23-78) and the backward pass
+    of train.py:126-131 on the kernels.  The nets run the bf16 hi/lo split here (fp32-grade products): the
+    loss gate is 1e-3 relative, the gradient gate 1e-3 relative L2 per tensor."""
 
     TC_D1 = _tc_mode("TRAIN_D1", 3)
     TC_ENH = _tc_mode("TRAIN_ENH", 3)
     TC_D2 = _tc_mode("TRAIN_D2", 3)
+    TC_BWD = _tc_mode("TRAIN_BWD", 3)
 
     def _prepare(self, device):
         m = self.model
@@ -427,12 +435,13 @@ class TrainEngine(FrameEngine):
         if fresh:   # train-mode BatchNorm needs the un-folded block convolution
             e = m.enhance
             self.w["e.blk_raw"] = ConvW(e.conv[0].weight.to(device), e.conv[0].bias.to(device))
+            self._wbwd = None
 
     # L_pred = x - denoise_1(x) without clamp (model.py:149-150)
-    def denoise1_residual(self, x, H, W):
+    def denoise1_residual(self, x, H, W, tag=""):
         w, ws, HW = self.w, self.ws, H * W
-        xp, a1, a2, d = (ws.get("xp", (HW, 4)), ws.get("a48a", (HW, 48)), ws.get("a48b", (HW, 48)),
-                         ws.get("d4", (HW, 4)))
+        xp, a1, a2, d = (ws.get("xp" + tag, (HW, 4)), ws.get("a48a" + tag, (HW, 48)), ws.get("a48b" + tag, (HW, 48)),
+                         ws.get("d4" + tag, (HW, 4)))
         ops.pack_nhwc([x], 3, 0.0, xp, 4, HW)
         ops.conv2d(w["d1.c1"], xp, 4, 4, 1, H, W, a1, 48, pad=(1, 1), act="lrelu", tc=self.TC_D1)
         ops.conv2d(w["d1.c2"], a1, 48, 48, 1, H, W, a2, 48, pad=(1, 1), act="lrelu", tc=self.TC_D1)
@@ -443,23 +452,23 @@ class TrainEngine(FrameEngine):
 
     def enhance_train(self, x, H3_wp, s3_wp, L2, H, W):
         """Enhancer.forward with BatchNorm in TRAIN mode (batch statistics, running stats updated three
-        times - model.py:60-67,74-81 under train.py:116), then H2 = clamp((x+eps)/s2, eps, 1)."""
+        times - model.py:60-67,74-81 under train.py:116), then H2 = clamp((x+eps)/s2, eps, 1).  Every
+        intermediate (pre-BN conv outputs, block outputs, batch statistics) is kept for the backward pass."""
         w, ws, HW = self.w, self.ws, H * W
         bn = self.model.enhance.conv[1]
-        ep, fa, fb, t = (ws.get("ep12", (HW, 12)), ws.get("f64a", (HW, 64)), ws.get("f64b", (HW, 64)),
-                         ws.get("f64t", (HW, 64)))
+        ep = ws.get("ep12", (HW, 12))
+        cur = [ws.get("e.cur%d" % k, (HW, 64)) for k in range(4)]
+        t = [ws.get("e.t%d" % k, (HW, 64)) for k in range(3)]
+        st = [ws.get("e.stats%d" % k, (128,), torch.float64) for k in range(3)]
         s4 = ws.get("s4", (HW, 4))
-        stats = ws.get("bn_stats", (128,), torch.float64)
         ops.pack_nhwc([H3_wp, s3_wp, L2], 3, 0.0, ep, 12, HW)
-        ops.conv2d(w["e.in"], ep, 12, 12, 1, H, W, fa, 64, pad=(1, 1), act="relu", tc=self.TC_ENH)
-        cur, nxt = fa, fb
-        for _ in range(3):
-            ops.conv2d(w["e.blk_raw"], cur, 64, 64, 1, H, W, t, 64, pad=(1, 1), tc=self.TC_ENH)
-            ops.bn_train(t, 64, nxt, 64, cur, 64, stats, bn.weight, bn.bias, bn.running_mean, bn.running_var,
-                         HW, 64, bn.eps, bn.momentum)
+        ops.conv2d(w["e.in"], ep, 12, 12, 1, H, W, cur[0], 64, pad=(1, 1), act="relu", tc=self.TC_ENH)
+        for k in range(3):
+            ops.conv2d(w["e.blk_raw"], cur[k], 64, 64, 1, H, W, t[k], 64, pad=(1, 1), tc=self.TC_ENH)
+            ops.bn_train(t[k], 64, cur[k + 1], 64, cur[k], 64, st[k], bn.weight, bn.bias, bn.running_mean,
+                         bn.running_var, HW, 64, bn.eps, bn.momentum)
             bn.num_batches_tracked += 1
-            cur, nxt = nxt, cur
-        ops.conv2d(w["e.out"], cur, 64, 64, 1, H, W, s4, 4, pad=(1, 1), act="sigmoid", tc=self.TC_ENH)
+        ops.conv2d(w["e.out"], cur[3], 64, 64, 1, H, W, s4, 4, pad=(1, 1), act="sigmoid", tc=self.TC_ENH)
         s2, H2 = torch.empty_like(x), torch.empty_like(x)
         ops.retinex_h2(x, s4, 4, s2, H2, HW, self.EPS)
         return s2, H2
@@ -473,9 +482,9 @@ class TrainEngine(FrameEngine):
         h, wd = H // 2, W // 2
         eps = self.EPS
         L11, L12 = ops.pair_downsample(x, eps)
-        L_pred1 = self.denoise1_residual(L11, h, wd)
-        L_pred2 = self.denoise1_residual(L12, h, wd)
-        L2 = self.denoise1_L2(x, H, W)
+        L_pred1 = self.denoise1_residual(L11, h, wd, ".1a")
+        L_pred2 = self.denoise1_residual(L12, h, wd, ".1b")
+        L2 = self.denoise1_L2(x, H, W, ".1f")
         if is_new_seq:
             H3_wp = s3_wp = torch.zeros_like(L2)
             H31_wp = H32_wp = s31_wp = s32_wp = torch.zeros_like(L11)
@@ -490,9 +499,9 @@ class TrainEngine(FrameEngine):
         s21, s22 = ops.pair_downsample(s2)
         H11 = ops.div_clamp(L11, 0.0, s21, eps, 1.0)
         H12 = ops.div_clamp(L12, 0.0, s22, eps, 1.0)
-        H13, s13 = self.denoise2_H3(H31_wp, s31_wp, H11, s21, h, wd)
-        H14, s14 = self.denoise2_H3(H32_wp, s32_wp, H12, s22, h, wd)
-        H3, s3 = self.denoise2_H3(H3_wp, s3_wp, H2, s2, H, W)
+        H13, s13 = self.denoise2_H3(H31_wp, s31_wp, H11, s21, h, wd, ".a")
+        H14, s14 = self.denoise2_H3(H32_wp, s32_wp, H12, s22, h, wd, ".b")
+        H3, s3 = self.denoise2_H3(H3_wp, s3_wp, H2, s2, H, W, ".f")
         H3_pred, H4_pred = torch.cat([H13, s13], 1), torch.cat([H14, s14], 1)
         d12 = ops.texture_diff(L_pred1, L_pred2)
         H3d1, H3d2 = ops.pair_downsample(H3)
@@ -500,6 +509,7 @@ class TrainEngine(FrameEngine):
         H1 = ops.div_clamp(L2, 0.0, s2, 0.0, 1.0)
         H2_blur, H3_blur = ops.blur21(H1), ops.blur21(H3)
         self.last_wp = (H3_wp, s3_wp)
+        self.ctx = dict(x=x, H=H, W=W, L11=L11, L12=L12, training=training)
         return (L_pred1, L_pred2, L2, s2, s21, s22, H2, H11, H12, H13, s13, H14, s14, H3, s3, H3_pred, H4_pred,
                 d12, dH3, H2_blur, H3_blur, H3d1, H3d2)
 
@@ -513,9 +523,10 @@ class TrainEngine(FrameEngine):
         ws = self.ws
         acc = torch.zeros(32, dtype=torch.float64, device=x.device)
         chansum = ws.get("chansum", (4,), torch.float64)
-        scr1, scr2 = ws.get("loss_scr1", (1, 3, H, W)), ws.get("loss_scr2", (1, 3, H, W))
+        ycc = ws.get("loss_ycc", (1, 3, H, W))
+        avg1, avg2 = ws.get("loss_avg1", (1, 3, H, W)), ws.get("loss_avg2", (1, 3, H, W))
         ops.loss_illum(L2, s2, is_WB, chansum, acc, 0)
-        ops.loss_smooth(L2, s2, scr1, acc, 2)
+        ops.loss_smooth(L2, s2, ycc, acc, 2)
         ops.loss_tv(s2, acc, 14)
         L11, L12 = ops.pair_downsample(x, 1e-9)       # loss.py:24,51: input + 1e-9
         den1, den2 = ops.pair_downsample(L2)
@@ -532,7 +543,7 @@ class TrainEngine(FrameEngine):
         ops.mse_sum(H2_blur, H3_blur, acc, 24)
         ops.mse_sum(s2, s3, acc, 25)
         ops.loss_inter(H3d1, H3d2, dH3, acc, 26)
-        ops.loss_var(H2, H3, scr1, scr2, acc, 28)
+        ops.loss_var(H2, H3, avg1, avg2, acc, 28)
         n3, nh = 3.0 * H * W, 3.0 * h * wd
         sm = sum(2.0 * acc[2 + i] / ((H - dy) * (W - abs(dx))) for i, (dy, dx) in enumerate(SMOOTH_OFFSETS))
         tv = 2.0 * (acc[14] / ((H - 1) * W) + acc[15] / (H * (W - 1)))
@@ -541,4 +552,166 @@ class TrainEngine(FrameEngine):
                  1000 * acc[20] / (2 * nh), 1000 * acc[21] / (2 * nh), 1000 * acc[22] / nh, 1000 * acc[23] / nh,
                  10000 * acc[24] / n3, 1000 * acc[25] / n3, 10000 * acc[26] / nh, 10000 * acc[27] / nh,
                  1000 * acc[28] / n3]
+        if getattr(self, "ctx", None) is not None:
+            self.ctx.update(outs=outs, is_WB=is_WB, L11e=L11, L12e=L12, den1=den1, den2=den2)
         return torch.stack(terms)
+
+    # ---- backward (train.py:129 loss.backward()) ----
+    def _prepare_bwd(self, device):
+        if getattr(self, "_wbwd", None) is not None:
+            return
+        m, w = self.model, {}
+        e, d1, d2 = m.enhance, m.denoise_1, m.denoise_2
+        w["e.out"] = ops.dgrad_weights(e.out_conv[0].weight.to(device), cin_pad=4)
+        w["e.blk"] = ops.dgrad_weights(e.conv[0].weight.to(device))
+        w["d1.c3"] = ops.dgrad_weights(d1.conv3.weight.to(device), cin_pad=4)
+        w["d1.c2"] = ops.dgrad_weights(d1.conv2.weight.to(device))
+        w["d2.c3"] = ops.dgrad_weights(d2.conv3.weight.to(device), cin_pad=8)
+        w["d2.c2"] = ops.dgrad_weights(d2.conv2.weight.to(device))
+        w["d2.c1"] = ops.dgrad_weights(d2.conv1.weight.to(device))
+        self._wbwd = w
+        if getattr(self, "_wg", None) is None:
+            fw = self.w
+            self._wg = {
+                "e.in": ops.WGrad(fw["e.in"], e.in_conv[0].weight.shape, device),
+                "e.blk": ops.WGrad(fw["e.blk_raw"], e.conv[0].weight.shape, device),
+                "e.out": ops.WGrad(fw["e.out"], e.out_conv[0].weight.shape, device),
+            }
+            for n, d in (("d1", d1), ("d2", d2)):
+                for c in ("1", "2", "3"):
+                    self._wg[f"{n}.c{c}"] = ops.WGrad(fw[f"{n}.c{c}"], getattr(d, "conv" + c).weight.shape, device)
+            self._bn_g = torch.zeros(2, 64, device=device)
+
+    def _denoise_bwd(self, n, tag, g_d, d_cs, H, W, cin_p, want_input_grad):
+        """Backward of one application of denoise_1 / denoise_2 given the NHWC gradient of its output.
+        Accumulates the weight gradients; returns the NHWC gradient of the packed input (denoise_2 only)."""
+        ws, wb, wg, HW, T = self.ws, self._wbwd, self._wg, H * W, self.TC_BWD
+        xin = ws.get(("xp" if n == "d1" else "dp12") + tag, (HW, cin_p))
+        a1, a2 = ws.get("a48a" + tag, (HW, 48)), ws.get("a48b" + tag, (HW, 48))
+        g2, g1 = ws.get("g48b", (HW, 48)), ws.get("g48a", (HW, 48))
+        wg[n + ".c3"].accumulate(a2, 48, g_d, d_cs, H, W, (0, 0))
+        ops.conv2d(wb[n + ".c3"], g_d, d_cs, d_cs, 1, H, W, g2, 48, tc=T)
+        ops.act_bwd(g2, 48, a2, 48, 48, "lrelu", HW)
+        wg[n + ".c2"].accumulate(a1, 48, g2, 48, H, W, (1, 1))
+        ops.conv2d(wb[n + ".c2"], g2, 48, 48, 1, H, W, g1, 48, pad=(1, 1), tc=T)
+        ops.act_bwd(g1, 48, a1, 48, 48, "lrelu", HW)
+        wg[n + ".c1"].accumulate(xin, cin_p, g1, 48, H, W, (1, 1))
+        if not want_input_grad:
+            return None
+        gin = ws.get("g12", (HW, cin_p))
+        ops.conv2d(wb[n + ".c1"], g1, 48, 48, 1, H, W, gin, cin_p, pad=(1, 1), tc=T)
+        return gin
+
+    def backward(self):
+        """Gradients of the summed loss w.r.t. the 20 trainable tensors (TRAIN_PARAMS order)."""
+        c = self.ctx
+        if c is None or "outs" not in c:
+            raise RuntimeError("backward() needs a preceding forward_train() + loss_terms()")
+        if not c["training"]:
+            raise NotImplementedError("backward through eval-mode BatchNorm is not part of train.py's step")
+        (L_pred1, L_pred2, L2, s2, s21, s22, H2, H11, H12, H13, s13, H14, s14, H3, s3, H3_pred, H4_pred,
+         d12, dH3, H2_blur, H3_blur, H3d1, H3d2) = c["outs"]
+        x, H, W = c["x"], c["H"], c["W"]
+        h, wd = H // 2, W // 2
+        HW, hw = H * W, h * wd
+        n3, nh = 3.0 * HW, 3.0 * hw
+        eps = self.EPS
+        dev = x.device
+        self._prepare_bwd(dev)
+        ws, wg = self.ws, self._wg
+        for g in wg.values():
+            g.zero()
+        self._bn_g.zero_()
+        # frame-level gradient planes (zeroed slab; kernels accumulate)
+        full = ws.get("gfull", (5, 1, 3, H, W))
+        half = ws.get("ghalf", (12, 1, 3, h, wd))
+        full.zero_()
+        half.zero_()
+        g_s2, g_H2, g_H3, g_s3, g_L2 = full[0], full[1], full[2], full[3], full[4]
+        (g_Lp1, g_Lp2, g_H13, g_s13, g_H14, g_s14, g_H3d1, g_H3d2, g_H11, g_H12, g_s21, g_s22) = half.unbind(0)
+        tf = [ws.get("bw_tf%d" % i, (1, 3, H, W)) for i in range(3)]
+        th = [ws.get("bw_th%d" % i, (1, 3, h, wd)) for i in range(2)]
+        # ---- loss adjoints (loss.py:46-77) ----
+        ops.loss_illum_bwd(L2, s2, c["is_WB"], ws.get("chansum", (4,), torch.float64), 700 * 2 / n3, 1000 * 2 / n3, g_s2)
+        ops.loss_smooth_bwd(ws.get("loss_ycc", (1, 3, H, W)), s2,
+                            [5 * 2.0 / ((H - dy) * (W - abs(dx))) for dy, dx in SMOOTH_OFFSETS], g_s2)
+        ops.loss_tv_bwd(s2, 1600 * 2.0 / ((H - 1) * W), 1600 * 2.0 / (H * (W - 1)), g_s2)
+        k1 = 1000 * 2 / nh
+        ops.mse_bwd(c["L11e"], L_pred2, k1, gb=g_Lp2)
+        ops.mse_bwd(c["L12e"], L_pred1, k1, gb=g_Lp1)
+        th[0].zero_()
+        th[1].zero_()
+        ops.mse_bwd(L_pred1, c["den1"], k1, ga=g_Lp1, gb=th[0])
+        ops.mse_bwd(L_pred2, c["den2"], k1, ga=g_Lp2, gb=th[1])
+        ops.pair_downsample_bwd(th[0], th[1], g_L2)
+        k2 = 1000 * 2 / (2 * nh)
+        ops.mse_bwd(H13, H12, k2, ga=g_H13)
+        ops.mse_bwd(s13, s22, k2, ga=g_s13)
+        ops.mse_bwd(H14, H11, k2, ga=g_H14)
+        ops.mse_bwd(s14, s21, k2, ga=g_s14)
+        ops.mse_bwd(H13, H3d1, k1, ga=g_H13, gb=g_H3d1)
+        ops.mse_bwd(H14, H3d2, k1, ga=g_H14, gb=g_H3d2)
+        tf[0].zero_()
+        ops.mse_bwd(H3_blur, H2_blur, 10000 * 2 / n3, ga=tf[0])
+        ops.blur21_bwd(tf[0], tf[1], g_H3)
+        ops.mse_bwd(s3, s2, 1000 * 2 / n3, ga=g_s3)
+        ops.loss_inter_bwd(H3d1, H3d2, dH3, 10000 * 2 / nh, th[0], th[1], g_H3d1, g_H3d2)
+        ops.loss_var_bwd(H2, H3, ws.get("loss_avg1", (1, 3, H, W)), ws.get("loss_avg2", (1, 3, H, W)), 1000 * 2 / n3,
+                         tf[0], tf[1], tf[2], g_H2, g_H3)
+        ops.pair_downsample_bwd(g_H3d1, g_H3d2, g_H3)
+        # ---- denoise_2, three applications (model.py:180-191); inputs H*, s* are NOT detached ----
+        for tag, hh, ww, gH, oH, gs, os_, dH, ds in ((".f", H, W, g_H3, H3, g_s3, s3, g_H2, g_s2),
+                                                     (".a", h, wd, g_H13, H13, g_s13, s13, g_H11, g_s21),
+                                                     (".b", h, wd, g_H14, H14, g_s14, s14, g_H12, g_s22)):
+            gd = ws.get("gd8", (hh * ww, 8))
+            ops.mask_pack([gH, gs], [oH, os_], 3, -1.0, eps, 1.0, gd, 8, hh * ww)
+            gin = self._denoise_bwd("d2", tag, gd, 8, hh, ww, 12, True)
+            ops.unpack_add(gin, 12, 6, 3, [dH, ds], hh * ww)
+        # ---- Retinex glue (model.py:169-177) ----
+        ops.div_clamp_bwd(c["L11"], 0.0, s21, g_H11, eps, 1.0, g_s21)
+        ops.div_clamp_bwd(c["L12"], 0.0, s22, g_H12, eps, 1.0, g_s22)
+        ops.pair_downsample_bwd(g_s21, g_s22, g_s2)
+        ops.div_clamp_bwd(x, eps, s2, g_H2, eps, 1.0, g_s2)
+        # ---- enhancer (model.py:74-81), BatchNorm in train mode, one shared block applied three times ----
+        bn = self.model.enhance.conv[1]
+        T = self.TC_BWD
+        s4 = ws.get("s4", (HW, 4))
+        cur = [ws.get("e.cur%d" % k, (HW, 64)) for k in range(4)]
+        t = [ws.get("e.t%d" % k, (HW, 64)) for k in range(3)]
+        st = [ws.get("e.stats%d" % k, (128,), torch.float64) for k in range(3)]
+        red = ws.get("bn_red", (128,), torch.float64)
+        gs4 = ws.get("gs4", (HW, 4))
+        ga, gb, gt = ws.get("g64a", (HW, 64)), ws.get("g64b", (HW, 64)), ws.get("g64t", (HW, 64))
+        ops.mask_pack([g_s2], [s2], 3, 1.0, 1e-4, 1.0, gs4, 4, HW)   # Enhancer clamps to [1e-4, 1] (model.py:80)
+        ops.act_bwd(gs4, 4, s4, 4, 4, "sigmoid", HW)
+        wg["e.out"].accumulate(cur[3], 64, gs4, 4, H, W, (1, 1))
+        ops.conv2d(self._wbwd["e.out"], gs4, 4, 4, 1, H, W, ga, 64, pad=(1, 1), tc=T)
+        dcur, dnxt = ga, gb
+        for k in (2, 1, 0):
+            ops.bn_train_bwd(t[k], 64, dcur, 64, st[k], red, bn.weight, bn.bias, HW, 64, bn.eps, gt, 64,
+                             self._bn_g[0], self._bn_g[1])
+            wg["e.blk"].accumulate(cur[k], 64, gt, 64, H, W, (1, 1))
+            ops.conv2d(self._wbwd["e.blk"], gt, 64, 64, 1, H, W, dnxt, 64, pad=(1, 1), epi="add", aux0=dcur,
+                       aux0_cs=64, tc=T)
+            dcur, dnxt = dnxt, dcur
+        ops.act_bwd(dcur, 64, cur[0], 64, 64, "relu", HW)
+        wg["e.in"].accumulate(ws.get("ep12", (HW, 12)), 12, dcur, 64, H, W, (1, 1))
+        # ---- denoise_1, three applications (model.py:149-152) ----
+        gd = ws.get("gd4", (HW, 4))
+        ops.mask_pack([g_L2], [L2], 3, -1.0, eps, 1.0, gd, 4, HW)
+        self._denoise_bwd("d1", ".1f", gd, 4, H, W, 4, False)
+        for tag, g in ((".1a", g_Lp1), (".1b", g_Lp2)):
+            gd = ws.get("gd4h", (hw, 4))
+            ops.mask_pack([g], [None], 3, -1.0, 0.0, 0.0, gd, 4, hw)
+            self._denoise_bwd("d1", tag, gd, 4, h, wd, 4, False)
+        # ---- parameter gradients in torch layout ----
+        out = []
+        for name in ("e.in", "e.blk"):
+            out += list(wg[name].grads())
+            if name == "e.blk":
+                out += [self._bn_g[0].clone(), self._bn_g[1].clone()]
+        out += list(wg["e.out"].grads())
+        for n in ("d1", "d2"):
+            for cc in ("1", "2", "3"):
+                out += list(wg[f"{n}.c{cc}"].grads())
+        return out

@@ -111,8 +111,8 @@ class Finetunemodel(nn.Module, _Recurrent):
 
 class Network(nn.Module, _Recurrent):
     """Zero-shot training model (model/model.py:84-259): parameter tree, recurrent state,
-    ``update_cache``, the 23-tensor training forward and the 17 loss terms run on the CUDA kernels.
-    The backward pass is the next scope row: ``_loss`` returns the value only."""
+    ``update_cache``, the 23-tensor training forward, the 17 loss terms and the backward pass of the
+    zero-shot training step run on the CUDA kernels."""
 
     def __init__(self, args):
         super().__init__()
@@ -157,12 +157,44 @@ class Network(nn.Module, _Recurrent):
         self.last_H3_wp, self.last_s3_wp = self.frame_engine().last_wp
         return outs
 
+    def trainable(self):
+        """The 20 trainable tensors in the order of engine.TRAIN_PARAMS."""
+        from zero_tig_b200.engine import TRAIN_PARAMS
+        named = dict(self.named_parameters())
+        return [named[k] for k in TRAIN_PARAMS]
+
     def _loss(self, input):
-        """LossFunction.forward over Network.forward (model.py:205-215).  Forward value only in this
-        round: the scalar has no autograd graph yet (the backward kernels are the next scope row)."""
+        """LossFunction.forward over Network.forward (model.py:205-215).  With autograd enabled the returned
+        scalar carries a graph node whose backward runs the CUDA backward pass and fills ``.grad`` of the 20
+        trainable tensors, so ``loss.backward()`` / ``clip_grad_norm_`` / ``optimizer.step()`` of train.py:126-131
+        work unchanged."""
+        params = self.trainable()
+        if torch.is_grad_enabled() and any(p.requires_grad for p in params):
+            return _ZeroTigLoss.apply(self, input, *params)
+        return self._loss_value(input)
+
+    def _loss_value(self, input):
         outs = self(input)
         with torch.no_grad():
             terms = self.frame_engine().loss_terms(input, outs, self.is_WB)
         self.last_loss_terms = terms
         self.update_H3(outs[13], outs[14])
         return terms.sum().float()
+
+
+class _ZeroTigLoss(torch.autograd.Function):
+    """Graph node of ``Network._loss``: forward = CUDA forward + 17 loss terms, backward = the hand-written
+    backward pass (engine.TrainEngine.backward).  The parameters are passed only so autograd routes the
+    gradients to them."""
+
+    @staticmethod
+    def forward(ctx, net, input, *params):
+        ctx.net = net
+        return net._loss_value(input)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        with torch.no_grad():
+            grads = ctx.net.frame_engine().backward()
+            grads = [g * grad_out.to(g.dtype) for g in grads]
+        return (None, None, *grads)

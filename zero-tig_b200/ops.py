@@ -289,3 +289,106 @@ def loss_inter(d1, d2, diff, acc, off):
 def loss_var(H2, H3, avg1, avg2, acc, off):
     check(lib().zt_loss_var_f32(_p(H2), _p(H3), _p(avg1), _p(avg2), H2.shape[1], H2.shape[2], H2.shape[3],
                                 _p(acc, off), _stream()), "loss_var")
+
+
+# ---------------------------------------------------------------------------------------
+# training backward (csrc/train_bwd.cu)
+# ---------------------------------------------------------------------------------------
+def dgrad_weights(weight, cin_pad=None):
+    """Weights of the data-gradient convolution of a stride-1 nn.Conv2d: spatially flipped, in/out
+    channels swapped, so dX = conv2d(dY, W') runs on the forward (tensor-core) convolution."""
+    return ConvW(weight.detach().transpose(0, 1).flip(2, 3).contiguous(), None, cin_pad=cin_pad)
+
+
+def mse_bwd(a, b, coef, ga=None, gb=None, add_a=0.0):
+    check(lib().zt_mse_bwd_f32(_p(a), _p(b), add_a, a.numel(), coef, _p(ga), _p(gb), _stream()), "mse_bwd")
+
+
+def loss_illum_bwd(L2, s2, is_WB, chansum, c0, c1, g_s2):
+    check(lib().zt_loss_illum_bwd_f32(_p(L2), _p(s2), int(is_WB), L2.shape[2] * L2.shape[3], _p(chansum), c0, c1,
+                                      _p(g_s2), _stream()), "loss_illum_bwd")
+
+
+def loss_smooth_bwd(ycc, s2, coefs, g_s2):
+    check(lib().zt_loss_smooth_bwd_f32(_p(ycc), _p(s2), s2.shape[2], s2.shape[3], (C.c_float * 12)(*coefs), _p(g_s2),
+                                       _stream()), "loss_smooth_bwd")
+
+
+def loss_tv_bwd(x, ch, cw, g):
+    check(lib().zt_loss_tv_bwd_f32(_p(x), x.shape[1], x.shape[2], x.shape[3], ch, cw, _p(g), _stream()), "loss_tv_bwd")
+
+
+def loss_inter_bwd(d1, d2, diff, coef, u1, u2, g1, g2):
+    check(lib().zt_loss_inter_bwd_f32(_p(d1), _p(d2), _p(diff), d1.shape[1], d1.shape[2], d1.shape[3], coef, _p(u1),
+                                      _p(u2), _p(g1), _p(g2), _stream()), "loss_inter_bwd")
+
+
+def loss_var_bwd(H2, H3, avg1, avg2, coef, t0, t1, t2, g_H2, g_H3):
+    check(lib().zt_loss_var_bwd_f32(_p(H2), _p(H3), _p(avg1), _p(avg2), H2.shape[1], H2.shape[2], H2.shape[3], coef,
+                                    _p(t0), _p(t1), _p(t2), _p(g_H2), _p(g_H3), _stream()), "loss_var_bwd")
+
+
+def blur21_bwd(g_in, tmp, g_out):
+    _, Cn, H, W = g_in.shape
+    check(lib().zt_blur21_bwd_f32(_p(g_in), _p(tmp), _p(g_out), blur_taps(), Cn, H, W, _stream()), "blur21_bwd")
+
+
+def pair_downsample_bwd(g1, g2, gx):
+    _, Cn, H, W = gx.shape
+    check(lib().zt_pair_downsample_bwd_f32(_p(g1), _p(g2), Cn, H, W, _p(gx), _stream()), "pair_downsample_bwd")
+
+
+def div_clamp_bwd(a, add, b, g_out, lo, hi, g_b):
+    check(lib().zt_div_clamp_bwd_f32(_p(a), add, _p(b), _p(g_out), a.numel(), lo, hi, _p(g_b), _stream()),
+          "div_clamp_bwd")
+
+
+def mask_pack(gs, outs, c_each, sign, lo, hi, out, cs, HW):
+    """out[p][k*c_each+c] = sign * gs[k][c][p] * [lo < outs[k][c][p] < hi]  (outs[k] None: no mask)."""
+    g = list(gs) + [None] * (2 - len(gs))
+    o = list(outs) + [None] * (2 - len(outs))
+    check(lib().zt_mask_pack_nhwc_f32(_p(g[0]), _p(o[0]), _p(g[1]), _p(o[1]), c_each, len(gs), sign, lo, hi, _p(out),
+                                      cs, HW, _stream()), "mask_pack")
+
+
+def unpack_add(g, cs, c_off, c_each, dsts, HW):
+    d = list(dsts) + [None] * (2 - len(dsts))
+    check(lib().zt_unpack_add_nchw_f32(_p(g), cs, c_off, c_each, len(dsts), _p(d[0]), _p(d[1]), HW, _stream()),
+          "unpack_add")
+
+
+def act_bwd(g, g_cs, y, y_cs, Cn, act, M):
+    check(lib().zt_act_bwd_nhwc_f32(_p(g), g_cs, _p(y), y_cs, Cn, ACT[act], M, _stream()), "act_bwd")
+
+
+def bn_train_bwd(x, x_cs, dout, d_cs, stats, red, gamma, beta, HW, Cn, eps, dx, dx_cs, dgamma, dbeta):
+    check(lib().zt_bn_train_bwd_nhwc_f32(_p(x), x_cs, _p(dout), d_cs, _p(stats), _p(red), _p(gamma), _p(beta), HW, Cn,
+                                         eps, _p(dx), dx_cs, _p(dgamma), _p(dbeta), _stream()), "bn_train_bwd")
+
+
+class WGrad:
+    """fp32 accumulator of one nn.Conv2d's weight / bias gradient in the kernel layout [kh][kw][cin_p][w_cs]."""
+
+    def __init__(self, wt: ConvW, weight_shape, device):
+        self.cout, self.cin, self.kh, self.kw = weight_shape
+        self.cin_p, self.w_cs = wt.cin, wt.w_cs
+        self.dw = torch.zeros(self.kh, self.kw, self.cin_p, self.w_cs, device=device)
+        self.db = torch.zeros(self.w_cs, device=device)
+
+    def zero(self):
+        self.dw.zero_()
+        self.db.zero_()
+
+    def accumulate(self, X, x_cs, G, g_cs, H, W, pad):
+        check(lib().zt_conv2d_wgrad_nhwc_f32(_p(X), x_cs, _p(G), g_cs, _p(self.dw), _p(self.db), H, W, self.kh, self.kw,
+                                             pad[0], pad[1], self.cin_p, self.cout, self.w_cs, _stream()), "wgrad")
+
+    def grads(self):
+        """(dweight [cout][cin][kh][kw], dbias [cout]) in torch's parameter layout."""
+        return (self.dw[:, :, :self.cin, :self.cout].permute(3, 2, 0, 1).contiguous(), self.db[:self.cout].clone())
+
+
+def clip_adam(param, grad, exp_avg, exp_avg_sq, sumsq, step, lr, betas, eps, weight_decay, max_norm, grad_scale=1.0):
+    check(lib().zt_clip_adam_f32(_p(param), _p(grad), _p(exp_avg), _p(exp_avg_sq), param.numel(), _p(sumsq),
+                                 grad_scale, max_norm, lr, betas[0], betas[1], eps, weight_decay, step, _stream()),
+          "clip_adam")
