@@ -254,6 +254,14 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, e2e_ms = t.tolist()
+    train = None
+    if not args.no_train:
+        tr_ms, tr_launches, tr_loss = train_step_bench(dev, world, sd)
+        train = {"workload": "zero-shot training step 960x540 (configs[2]): _loss fwd (RAFT + warp + nets + 17 loss "
+                             "terms), CUDA backward, flat-gradient all-reduce (NCCL, world>1), fused clip+Adam; one "
+                             "clip per rank", "value": world * 1e3 / tr_ms, "unit": "frames/s", "ms_per_step": tr_ms,
+                 "gpu_launches_per_step": int(tr_launches), "steps": 6, "warmup": 3, "last_loss": tr_loss,
+                 "collective": "1 x all_reduce(sum) of 92620 fp32 per step" if world > 1 else "none (1 GPU)"}
 
     out = None
     if rank == 0:
@@ -306,6 +314,8 @@ def run_b200(args):
                     "d2h_bytes_per_step": 2 * 3 * H * W * 4},
             "gpu_launches": int(launches), "roofline": roof, "tensor_kernels": [tensor], "hbm_kernels": hbm,
         }
+        if train is not None:
+            out["train_step"] = train
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(sd)
     if world > 1:
@@ -313,6 +323,49 @@ def run_b200(args):
         dist.destroy_process_group()
     if out is not None:
         print(json.dumps(out))
+
+
+TRAIN_H, TRAIN_W = 540, 960
+
+
+def train_step_bench(dev, world, sd, steps=6, warmup=2):
+    """configs[2]: zero-shot training steps (Network._loss forward incl. RAFT + warp, CUDA backward, one
+    all-reduce of the flat gradient buffer when world > 1, fused clip + Adam) on a synthetic 960x540 clip,
+    one clip per rank.  Returns (ms_per_step max over ranks, launches per step)."""
+    import torch.distributed as dist
+    from zero_tig_b200 import _lib, synth
+    from zero_tig_b200.model.model import Network
+    from zero_tig_b200.optim import ClipAdam
+    rank = int(os.environ.get("RANK", "0"))
+    net = Network(synth.make_args(of_scale=OF_SCALE)).to(dev)
+    net.load_state_dict(sd)
+    net.train()
+    opt = ClipAdam(net.trainable(), lr=1e-4, weight_decay=3e-4, max_norm=5.0)
+    clip = synth.synthetic_clip(warmup + steps + 1, TRAIN_H, TRAIN_W, seed=100 + rank).to(dev)
+
+    def step(i):
+        net.is_new_seq = (i == 0)
+        opt.zero_grad()
+        loss = net._loss(clip[i:i + 1])
+        loss.backward()
+        opt.step()
+        return loss
+    for i in range(warmup + 1):
+        step(i)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    l0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        loss = step(warmup + 1 + i)
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / steps], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.item(), (_lib.launch_count() - l0) // steps, float(loss.detach())
 
 
 def cpu_baseline(sd):
@@ -340,6 +393,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-train", action="store_true", help="skip the configs[2] training-step measurement")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
