@@ -167,6 +167,14 @@ class OpTimer:
                     res = 1 if k.get("epi", "plain") in ("add", "add_relu") else 0
                     self.bytes[tag] = self.bytes.get(tag, 0) + 4.0 * (Bn * Hn * Wn * wt.cin + M * wt.cout * (1 + res))
                     self.flops[tag] = self.flops.get(tag, 0) + 2.0 * M * wt.cout * wt.cin * wt.kh * wt.kw
+                if _n == "conv2d_bf16":
+                    wt, cin_s, Hn, Wn, ocs = a[0], a[2], a[3], a[4], a[6]
+                    tag = "conv_frame"
+                    cout, cin_r = wt.w_raw.shape[0], wt.w_raw.shape[1]
+                    M = Hn * Wn
+                    byt = M * (2.0 * cin_s + (4.0 if k.get("out_f32") else 2.0) * ocs + (2.0 * cout if k.get("res") is not None else 0.0))
+                    self.bytes[tag] = self.bytes.get(tag, 0) + byt
+                    self.flops[tag] = self.flops.get(tag, 0) + 2.0 * M * cout * cin_r * wt.kh * wt.kw
                 self.rec.setdefault(tag, []).append((e0, e1))
                 return r
             setattr(self.ops, n, wrap)
@@ -267,7 +275,7 @@ def run_b200(args):
     if rank == 0:
         pk = peaks()
         # ---- per-kernel pass (rank 0): shares + roofline of the dominant kernels ----
-        with OpTimer(ops, ["conv2d", "warp_pair", "corr_lookup", "avgpool2", "instnorm"]) as ot:
+        with OpTimer(ops, ["conv2d", "conv2d_bf16", "warp_pair", "corr_lookup", "avgpool2", "instnorm"]) as ot:
             nprof = min(K, 5)
             for i in range(nprof):
                 step_dev(i)
@@ -277,14 +285,14 @@ def run_b200(args):
         warp_ms = tot["warp_pair"][0] / nprof
         look_ms = tot["corr_lookup"][0] / tot["corr_lookup"][1]
         corr_ms = (tot["corr_volume"][0] + tot["avgpool2"][0]) / nprof
-        # dominant kernel: the tcgen05 convolutions of the three full-resolution Retinex nets.  With
-        # fp32 NHWC activations in HBM they sit below the ridge (64->64 3x3: 96 flop/B vs ~211), so
-        # the bound is HBM: algorithmic bytes = every input/output/residual activation once.
+        # the tcgen05 convolutions of the three full-resolution Retinex nets (conv_tma_kernel: bf16 NHWC
+        # activations moved by TMA).  Algorithmic bytes = every input/output/residual activation once;
+        # algorithmic flops = 2*M*cout*cin*taps of the reference layers (no padding counted).
         fb = ot.bytes["conv_frame"] / nprof
         gbs = fb / frame_ms / 1e6
         nl = tot["conv_frame"][1] / nprof
-        roof = {"bound": "hbm", "kernel": "conv_tc_kernel (tcgen05 implicit-GEMM conv), the %d full-resolution "
-                                          "launches of a frame" % nl,
+        roof = {"bound": "hbm", "kernel": "conv_tma_kernel (TMA-fed tcgen05 implicit-GEMM conv, bf16 activations), the %d "
+                                          "full-resolution launches of a frame" % nl,
                 "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
                 "traffic": TRAFFIC_PER_LAUNCH, "algorithmic_bytes_per_launch": fb / nl,
                 "peak_source": pk["src"] + " copy bandwidth", "ms_per_frame": frame_ms,
@@ -304,7 +312,7 @@ def run_b200(args):
         out = {
             "metric": METRIC, "value": world * K / (ms / 1e3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16 tensor-core products (hi/lo split in RAFT), f32 accumulate/storage", "data": "synthetic",
+            "dtype": "bf16 tensor-core products, f32 accumulate (Retinex nets: bf16 activations; RAFT: bf16 hi/lo split, f32 storage)", "data": "synthetic",
             "config": {"workload": "RLV inference 1920x1080 (configs[1]), of_scale 3, 12 RAFT iters, steady state, "
                                    "synthetic %d-frame clip per rank" % n_frames,
                        "l2": "per-frame working set (>2 GB of activations) exceeds the 126 MB L2; no explicit flush",

@@ -153,6 +153,24 @@ int zt_retinex_h5_f32(const float* H2, const float* s2, const float* d, int d_cs
 /* save_images quantisation, predict.py:57-61: clip(x*255,0,255) -> uint8 (truncate), HWC */
 int zt_quantize_u8_hwc(const float* x, uint8_t* out, int C, int64_t HW, void* stream);
 
+/* ---- Retinex networks at full resolution: TMA-fed tcgen05 convolution over bf16 NHWC activations ----
+ * Replaces the nn.Conv2d layers of Denoise_1 / Enhancer / Denoise_2 (model/model.py:24-28,40-44,74-81) in
+ * inference: stride 1, 3x3 (pad 1) or 1x1, cin <= 64 (multiple of 8), cout <= 64, batch 1.
+ * in: bf16 [H*W][cin]; weight: bf16 [tap][BN=ceil16(cout)][64 ch], 128-byte swizzled rows (host packs);
+ * out: bf16 [H*W][out_cs] (out_f32 = 0; optional bf16 residual: out = res + act(conv + bias)) or
+ * fp32 [H*W][out_cs] with out_cs 4 or 8 (out_f32 = 1: the 3- and 6-channel heads). act = ZT_ACT_*. */
+typedef struct ZtConvBf16 {
+  const void* in; int cin;
+  const void* weight; const float* bias;
+  void* out; int out_cs; int out_f32;
+  const void* res; int res_cs;
+  int H; int W; int cout; int kh; int kw; int act;
+} ZtConvBf16;
+int zt_conv2d_bf16_tma(const ZtConvBf16* desc, void* stream);
+/* NCHW fp32 planes (+add) -> bf16 NHWC [HW][cs], cs = 8 or 16, zero padded (virtual torch.cat, model.py:313,326,334) */
+int zt_pack_nhwc_bf16(const float* s0, const float* s1, const float* s2, const float* s3, int c_each, int nsrc,
+                      float add, void* out, int cs, int64_t HW, void* stream);
+
 /* ---- training path: Network.forward (model/model.py:144-203) and loss.py -------------------
  * NCHW fp32, batch 1.  Reduction entry points ADD raw sums into fp64 accumulators the caller
  * zeroes; the host turns them into the 17 weighted terms of LossFunction.forward. */

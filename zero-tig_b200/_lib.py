@@ -27,6 +27,16 @@ class ZtConv(C.Structure):
     ]
 
 
+class ZtConvBf16(C.Structure):
+    _fields_ = [
+        ("in_", c_fp), ("cin", C.c_int),
+        ("weight", c_fp), ("bias", c_fp),
+        ("out", c_fp), ("out_cs", C.c_int), ("out_f32", C.c_int),
+        ("res", c_fp), ("res_cs", C.c_int),
+        ("H", C.c_int), ("W", C.c_int), ("cout", C.c_int), ("kh", C.c_int), ("kw", C.c_int), ("act", C.c_int),
+    ]
+
+
 I, L, F, P = C.c_int, C.c_int64, C.c_float, C.c_void_p
 IP = C.POINTER(C.c_int)
 
@@ -35,6 +45,8 @@ SIGNATURES = {
     "zt_conv2d_nhwc_f32": [C.POINTER(ZtConv), P],
     "zt_conv2d_tc_nhwc": [C.POINTER(ZtConv), I, I, P],
     "zt_debug_set_tc_trace": [P, I],
+    "zt_conv2d_bf16_tma": [C.POINTER(ZtConvBf16), P],
+    "zt_pack_nhwc_bf16": [P, P, P, P, I, I, F, P, I, L, P],
     "zt_pack_tc_rows_f32": [P, I, I, I, I, P, P],
     "zt_instnorm_nhwc_f32": [P, I, P, I, P, I, P, I, I, I, F, I, I, P],
     "zt_transpose_f32": [P, I, I, I, P, I, P],

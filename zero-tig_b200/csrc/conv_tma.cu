@@ -1,0 +1,399 @@
+// Full-resolution convolutions of the three Retinex networks (model/model.py:15-81) as a TMA-fed
+// tcgen05 implicit GEMM over bf16 NHWC activations.
+//
+// Why a second tensor-core kernel: conv_tc.cu keeps fp32 activations and converts them in producer
+// warps; at 1080p that kernel is bound by CUDA-core instruction issue and by tap-shifted operand views
+// that straddle two swizzle atoms (ncu: 10 % tensor pipe, 22 % DRAM, profiles/r01_ncu_conv_tc_*.txt).
+// Here the activations between layers are bf16 (the MMA consumed bf16 anyway), so
+//   * one elected thread moves the input with TMA (cp.async.bulk.tensor.3d, SWIZZLE_128B, zero fill
+//     outside the image = the convolution's zero padding): no producer warps, no conversions;
+//   * the 16x8 pixel tile is loaded as kw copies shifted by one pixel, each a [rows][8 px][64 ch] box
+//     whose 8-pixel rows are exactly one 1024 B swizzle atom: every filter tap (ky,kx) is the view
+//     "copy kx, starting ky atoms in" - always atom aligned (58 clk per M128 K16 MMA instead of 114);
+//   * weights (<= 72 KB) stay resident in shared memory, accumulators are double buffered in TMEM,
+//     8 epilogue warps apply bias / activation / residual and write bf16 (or the small fp32 heads).
+// GEMM view: M = 128 pixels (16 rows x 8), N = cout (<= 64), K = taps x 64 channels (cin <= 64).
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <algorithm>
+#include <map>
+#include <mutex>
+#include <tuple>
+#include "common.cuh"
+#include "tc_ptx.cuh"
+
+namespace zt {
+
+constexpr int TM_TW = 8, TM_TH = 16;
+constexpr int TM_THREADS = 320;           // warps 0-7 epilogue, 8 MMA issuer, 9 TMA / weight loader
+constexpr int TM_W_MMA = 8, TM_W_LOAD = 9;
+constexpr int TM_BAR_BYTES = 1024;
+
+struct TmGeom {
+  int BN, kh, kw, nks, rows;              // rows = TM_TH + kh - 1
+  int tiles_x, S, NA, tmem_cols;
+  uint32_t copy_bytes, a_stage, w_tap, w_bytes;
+};
+struct TmArgs {
+  const uint8_t* weight;                  // [tap][BN][128 B] bf16, swizzled
+  const float* bias;
+  void* out;
+  int out_cs;
+  const __nv_bfloat16* res;
+  int res_cs;
+  int H, W, cout, ph, pw;
+};
+
+__device__ __forceinline__ float tm_act(float v, int act) {
+  if (act == ZT_ACT_RELU) return fmaxf(v, 0.f);
+  if (act == ZT_ACT_LRELU02) return v > 0.f ? v : 0.2f * v;
+  if (act == ZT_ACT_SIGMOID) return 1.f / (1.f + expf(-v));
+  return v;
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+// OUT: 0 = bf16 out, 1 = bf16 out with residual (out = res + act(v)), 2 = fp32 out (cout <= 8)
+template <int OUT, int ACT>
+__global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_constant__ CUtensorMap tmap,
+                                                                 const TmArgs a, const TmGeom g) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TM_BAR_BYTES - 16);
+  uint8_t* smA = smem + TM_BAR_BYTES;
+  uint8_t* smW = smA + (size_t)g.NA * g.a_stage;
+  const uint32_t bar0 = smem_u32(smem);
+  const int NA = g.NA;
+  auto fullA = [&](uint32_t s) { return bar0 + 8u * s; };
+  auto emptyA = [&](uint32_t s) { return bar0 + 8u * (NA + s); };
+  const uint32_t fullW = bar0 + 8u * (2 * NA);
+  auto accFull = [&](uint32_t s) { return bar0 + 8u * (2 * NA + 1 + s); };
+  auto accEmpty = [&](uint32_t s) { return bar0 + 8u * (2 * NA + 3 + s); };
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int S = g.S;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < NA; ++s) { mbar_init(fullA(s), 1); mbar_init(emptyA(s), 1); }
+    mbar_init(fullW, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(accFull(s), 1); mbar_init(accEmpty(s), 256); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == TM_W_MMA) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 ::"r"(smem_u32(tmem_slot)), "r"((uint32_t)g.tmem_cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < 8) {
+    // ===================== epilogue =====================
+    // thread = one pixel (TMEM lane) x 32 consecutive output channels of its half
+    const int quad = warp & 3, half = warp >> 2;
+    const int c0 = half * 32;
+    const bool has_cols = c0 < g.BN;
+    const bool second16 = c0 + 16 < g.BN;
+    float bias[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) bias[i] = (a.bias && c0 + i < a.cout) ? __ldg(a.bias + c0 + i) : 0.f;
+    uint32_t lt = 0;
+    for (int t = blockIdx.x; t < S; t += gridDim.x, ++lt) {
+      const int tyi = t / g.tiles_x, txi = t - tyi * g.tiles_x;
+      const int oy = tyi * TM_TH + quad * 4 + (lane >> 3), ox = txi * TM_TW + (lane & 7);
+      const bool ok = has_cols && oy < a.H && ox < a.W;
+      const int64_t pix = (int64_t)oy * a.W + ox;
+      const uint32_t buf = lt & 1;
+      uint4 rv[4];
+      if (OUT == 1) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          rv[j] = make_uint4(0u, 0u, 0u, 0u);
+          if (ok && c0 + 8 * j < a.cout) rv[j] = __ldg(reinterpret_cast<const uint4*>(a.res + pix * a.res_cs + c0 + 8 * j));
+        }
+      }
+      mbar_wait(accFull(buf), (lt >> 1) & 1);
+      tc_fence_after();
+      uint32_t v[32];
+      if (has_cols) {
+        const uint32_t taddr = tmem_base + buf * (uint32_t)g.BN + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0;
+        uint32_t v0[16], v1[16];
+        tmem_ld16(taddr, v0);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = v0[i];
+        if (second16) {
+          tmem_ld16(taddr + 16, v1);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[16 + i] = v1[i];
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[16 + i] = 0u;
+        }
+      }
+      // the accumulator is in registers: hand the TMEM buffer back before the stores
+      tc_fence_before();
+      mbar_arrive(accEmpty(buf));
+      if (!ok) continue;
+      if (OUT == 2) {
+        float* o = reinterpret_cast<float*>(a.out) + pix * a.out_cs;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          if (4 * j < a.out_cs) {
+            float r[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int c = 4 * j + e;
+              r[e] = c < a.cout ? tm_act(__uint_as_float(v[c]) + bias[c], ACT) : 0.f;
+            }
+            *reinterpret_cast<float4*>(o + 4 * j) = make_float4(r[0], r[1], r[2], r[3]);
+          }
+        }
+      } else {
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(a.out) + pix * a.out_cs + c0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (c0 + 8 * j < a.cout) {
+            float r[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) r[e] = tm_act(__uint_as_float(v[8 * j + e]) + bias[8 * j + e], ACT);
+            if (OUT == 1) {
+              const uint32_t rw[4] = {rv[j].x, rv[j].y, rv[j].z, rv[j].w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&rw[e]);
+                r[2 * e] += __low2float(h);
+                r[2 * e + 1] += __high2float(h);
+              }
+            }
+            *reinterpret_cast<uint4*>(o + 8 * j) = make_uint4(pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]),
+                                                              pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7]));
+          }
+        }
+      }
+    }
+  } else if (warp == TM_W_MMA) {
+    // ===================== MMA issuer =====================
+    const uint32_t BN = g.BN;
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((BN >> 3) << 17) | (8u << 24);
+    const uint64_t desc0 = make_desc(0, 1024u);
+    const uint32_t dhi = (uint32_t)(desc0 >> 32), dlo = (uint32_t)desc0;
+    const uint32_t smA16 = smem_u32(smA) >> 4, smW16 = smem_u32(smW) >> 4;
+    const uint32_t a_stage16 = g.a_stage >> 4, copy16 = g.copy_bytes >> 4, wtap16 = g.w_tap >> 4;
+    const uint32_t kh = g.kh, kw = g.kw, nks = g.nks;
+    mbar_wait(fullW, 0);
+    tc_fence_after();
+    uint32_t lt = 0, sa = 0, pa = 0;
+    for (int t = blockIdx.x; t < S; t += gridDim.x, ++lt) {
+      const uint32_t buf = lt & 1;
+      mbar_wait(accEmpty(buf), ((lt >> 1) & 1) ^ 1);
+      mbar_wait(fullA(sa), pa);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t tmem_d = tmem_base + buf * BN;
+        uint32_t acc = 0, blo = dlo + smW16;
+        const uint32_t abase = dlo + smA16 + sa * a_stage16;
+        for (uint32_t ky = 0; ky < kh; ++ky) {
+          for (uint32_t kx = 0; kx < kw; ++kx, blo += wtap16) {
+            const uint32_t alo = abase + kx * copy16 + ky * 64u;      // ky atoms of 1024 B
+            for (uint32_t ks = 0; ks < nks; ++ks) {
+              tc_mma_bf16_lh(tmem_d, alo + 2 * ks, dhi, blo + 2 * ks, dhi, idesc, acc);
+              acc = 1;
+            }
+          }
+        }
+        tc_commit(emptyA(sa));
+        tc_commit(accFull(buf));
+      }
+      __syncwarp();
+      if (++sa == (uint32_t)NA) { sa = 0; pa ^= 1; }
+    }
+  } else {
+    // ===================== loader: weights once, then one TMA box per kx copy per tile =====================
+    if (lane == 0) {
+      tma_prefetch_desc(&tmap);
+      if ((int)blockIdx.x < S) {
+        mbar_arrive_expect_tx(fullW, g.w_bytes);
+        const uint32_t ntaps = g.kh * g.kw;
+        for (uint32_t it = 0; it < ntaps; ++it)
+          bulk_g2s(smem_u32(smW + it * g.w_tap), a.weight + (size_t)it * g.w_tap, g.w_tap, fullW);
+      }
+      uint32_t sa = 0, pa = 1;
+      for (int t = blockIdx.x; t < S; t += gridDim.x) {
+        const int tyi = t / g.tiles_x, txi = t - tyi * g.tiles_x;
+        mbar_wait(emptyA(sa), pa);
+        mbar_arrive_expect_tx(fullA(sa), g.a_stage);
+        for (int kx = 0; kx < g.kw; ++kx)
+          tma_load_3d(smem_u32(smA + sa * g.a_stage + kx * g.copy_bytes), &tmap, 0, txi * TM_TW + kx - a.pw,
+                      tyi * TM_TH - a.ph, fullA(sa));
+        if (++sa == (uint32_t)NA) { sa = 0; pa ^= 1; }
+      }
+    }
+    __syncwarp();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == TM_W_MMA) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)g.tmem_cols)
+                 : "memory");
+  }
+}
+
+// NCHW fp32 planes (+add) -> bf16 NHWC [HW][cs] (cs = 8 or 16), zero padded: the first-layer inputs
+// (virtual torch.cat of model.py:313,326,334)
+template <int CS>
+__global__ void __launch_bounds__(256) pack_nhwc_bf16_kernel(const float* __restrict__ s0, const float* __restrict__ s1,
+                                                             const float* __restrict__ s2, const float* __restrict__ s3,
+                                                             int c_each, int nsrc, float add,
+                                                             __nv_bfloat16* __restrict__ out, int64_t HW) {
+  const float* src[4] = {s0, s1, s2, s3};
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < HW; p += (int64_t)gridDim.x * blockDim.x) {
+    float v[CS];
+#pragma unroll
+    for (int c = 0; c < CS; ++c) v[c] = 0.f;
+    int ch = 0;
+    for (int s = 0; s < nsrc; ++s)
+      for (int c = 0; c < c_each; ++c, ++ch) {
+        const float x = __ldg(src[s] + c * HW + p) + add;
+#pragma unroll
+        for (int k = 0; k < CS; ++k)
+          if (k == ch) v[k] = x;
+      }
+    uint4* o = reinterpret_cast<uint4*>(out + p * CS);
+#pragma unroll
+    for (int j = 0; j < CS / 8; ++j)
+      o[j] = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                        pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+  }
+}
+
+// ---- host: tensor-map cache ----
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+    (void)cudaGetLastError();
+  }
+  return fn;
+}
+static std::mutex g_tm_mu;
+static std::map<std::tuple<const void*, int, int, int, int>, CUtensorMap> g_tm_cache;
+
+static int get_tensor_map(const void* base, int C, int W, int H, int rows, CUtensorMap* out) {
+  std::lock_guard<std::mutex> lk(g_tm_mu);
+  auto key = std::make_tuple(base, C, W, H, rows);
+  auto it = g_tm_cache.find(key);
+  if (it != g_tm_cache.end()) { *out = it->second; return ZT_OK; }
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) { set_error("conv_bf16_tma: cuTensorMapEncodeTiled is unavailable (no CUDA driver)"); return ZT_ERR_CUDA; }
+  const cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H};
+  const cuuint64_t strides[2] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2};
+  const cuuint32_t box[3] = {64u, (cuuint32_t)TM_TW, (cuuint32_t)rows};
+  const cuuint32_t estr[3] = {1u, 1u, 1u};
+  CUtensorMap m;
+  const CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("conv_bf16_tma: cuTensorMapEncodeTiled failed (%d)", (int)r); return ZT_ERR_CUDA; }
+  if (g_tm_cache.size() > 256) g_tm_cache.clear();
+  g_tm_cache[key] = m;
+  *out = m;
+  return ZT_OK;
+}
+
+}  // namespace zt
+
+extern "C" int zt_pack_nhwc_bf16(const float* s0, const float* s1, const float* s2, const float* s3, int c_each,
+                                 int nsrc, float add, void* out, int cs, int64_t HW, void* stream) {
+  using namespace zt;
+  ZT_REQUIRE(s0 && out && nsrc >= 1 && nsrc <= 4 && c_each >= 1 && c_each * nsrc <= cs && HW > 0, "pack_nhwc_bf16: bad args");
+  ZT_REQUIRE((nsrc < 2 || s1) && (nsrc < 3 || s2) && (nsrc < 4 || s3), "pack_nhwc_bf16: missing source");
+  ZT_REQUIRE(cs == 8 || cs == 16, "pack_nhwc_bf16: cs must be 8 or 16 (got %d)", cs);
+  const int blocks = (int)std::min<int64_t>(ceil_div64(HW, 256), 16 * kNumSMs);
+  if (cs == 8)
+    pack_nhwc_bf16_kernel<8><<<blocks, 256, 0, (cudaStream_t)stream>>>(s0, s1, s2, s3, c_each, nsrc, add,
+                                                                       (__nv_bfloat16*)out, HW);
+  else
+    pack_nhwc_bf16_kernel<16><<<blocks, 256, 0, (cudaStream_t)stream>>>(s0, s1, s2, s3, c_each, nsrc, add,
+                                                                        (__nv_bfloat16*)out, HW);
+  return check_launch("pack_nhwc_bf16_kernel");
+}
+
+extern "C" int zt_conv2d_bf16_tma(const ZtConvBf16* dp, void* stream) {
+  using namespace zt;
+  ZT_REQUIRE(dp != nullptr, "conv_bf16_tma: null descriptor");
+  const ZtConvBf16& d = *dp;
+  ZT_REQUIRE(d.in && d.weight && d.out, "conv_bf16_tma: null pointer");
+  ZT_REQUIRE((d.kh == 1 || d.kh == 3) && d.kw == d.kh, "conv_bf16_tma: 1x1 or 3x3 only (got %dx%d)", d.kh, d.kw);
+  ZT_REQUIRE(d.cin >= 8 && d.cin <= 64 && (d.cin & 7) == 0, "conv_bf16_tma: cin=%d must be a multiple of 8 in [8,64]", d.cin);
+  ZT_REQUIRE(d.cout >= 1 && d.cout <= 64, "conv_bf16_tma: cout=%d must be <= 64", d.cout);
+  ZT_REQUIRE(d.H > 0 && d.W > 0 && (int64_t)d.H * d.W < (1ll << 31), "conv_bf16_tma: bad dims");
+  ZT_REQUIRE(((uintptr_t)d.in & 15) == 0 && ((uintptr_t)d.weight & 15) == 0 && ((uintptr_t)d.out & 15) == 0,
+             "conv_bf16_tma: pointers must be 16-byte aligned");
+  if (d.out_f32) {
+    ZT_REQUIRE(d.cout <= 8 && (d.out_cs == 4 || d.out_cs == 8) && d.out_cs >= d.cout && !d.res,
+               "conv_bf16_tma: fp32 output needs cout <= 8, out_cs 4 or 8, no residual");
+  } else {
+    ZT_REQUIRE((d.cout & 7) == 0 && (d.out_cs & 7) == 0 && d.out_cs >= d.cout, "conv_bf16_tma: bf16 output needs cout, out_cs %% 8 == 0");
+    ZT_REQUIRE(!d.res || ((d.res_cs & 7) == 0 && ((uintptr_t)d.res & 15) == 0), "conv_bf16_tma: bad residual");
+  }
+  TmGeom g;
+  g.BN = ceil_div(d.cout, 16) * 16;
+  g.kh = d.kh; g.kw = d.kw;
+  g.nks = ceil_div(d.cin, 16);
+  g.rows = TM_TH + d.kh - 1;
+  g.tiles_x = ceil_div(d.W, TM_TW);
+  g.S = g.tiles_x * ceil_div(d.H, TM_TH);
+  g.copy_bytes = (uint32_t)g.rows * 1024u;
+  g.a_stage = g.copy_bytes * d.kw;
+  g.w_tap = (uint32_t)g.BN * 128u;
+  g.w_bytes = g.w_tap * d.kh * d.kw;
+  g.tmem_cols = 32;
+  while (g.tmem_cols < 2 * g.BN) g.tmem_cols <<= 1;
+  const size_t budget = 226 * 1024 - TM_BAR_BYTES - g.w_bytes;
+  g.NA = (int)std::min<size_t>(4, budget / g.a_stage);
+  ZT_REQUIRE(g.NA >= 2, "conv_bf16_tma: tile does not fit shared memory");
+  const size_t smem = TM_BAR_BYTES + (size_t)g.NA * g.a_stage + g.w_bytes;
+  CUtensorMap tmap;
+  if (int e = get_tensor_map(d.in, d.cin, d.W, d.H, g.rows, &tmap)) return e;
+  TmArgs a;
+  a.weight = (const uint8_t*)d.weight; a.bias = d.bias; a.out = d.out; a.out_cs = d.out_cs;
+  a.res = (const __nv_bfloat16*)d.res; a.res_cs = d.res_cs;
+  a.H = d.H; a.W = d.W; a.cout = d.cout; a.ph = d.kh / 2; a.pw = d.kw / 2;
+  const int gx = std::min(kNumSMs, g.S);
+  cudaStream_t st = (cudaStream_t)stream;
+#define ZT_TM_LAUNCH(OUT, ACT)                                                                              \
+  do {                                                                                                      \
+    static bool attr_done = false;                                                                          \
+    if (!attr_done) {                                                                                       \
+      ZT_CUDA(cudaFuncSetAttribute(conv_tma_kernel<OUT, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+                                   227 * 1024));                                                            \
+      attr_done = true;                                                                                     \
+    }                                                                                                       \
+    conv_tma_kernel<OUT, ACT><<<gx, TM_THREADS, smem, st>>>(tmap, a, g);                                    \
+    return check_launch("conv_tma_kernel");                                                                 \
+  } while (0)
+  if (d.out_f32) {
+    if (d.act == ZT_ACT_NONE) ZT_TM_LAUNCH(2, ZT_ACT_NONE);
+    if (d.act == ZT_ACT_SIGMOID) ZT_TM_LAUNCH(2, ZT_ACT_SIGMOID);
+  } else if (d.res) {
+    if (d.act == ZT_ACT_RELU) ZT_TM_LAUNCH(1, ZT_ACT_RELU);
+  } else {
+    if (d.act == ZT_ACT_RELU) ZT_TM_LAUNCH(0, ZT_ACT_RELU);
+    if (d.act == ZT_ACT_LRELU02) ZT_TM_LAUNCH(0, ZT_ACT_LRELU02);
+  }
+  set_error("conv_bf16_tma: unsupported output/activation combination (out_f32=%d res=%d act=%d)", d.out_f32,
+            d.res != nullptr, d.act);
+  return ZT_ERR_ARG;
+}

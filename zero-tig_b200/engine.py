@@ -269,9 +269,10 @@ class FrameEngine:
     # plain bf16 tensor-core products for the three Retinex nets: measured 93 dB PSNR / 2e-4 px
     # EPE against the fp32 path over a 12-frame recurrence (profiles/r01_precision_sweep.txt),
     # far inside the 50 dB / 0.01 px gates.  RAFT itself needs the hi/lo split (0.07 px in bf16).
-    TC_D1 = _tc_mode("D1", 1)
-    TC_ENH = _tc_mode("ENH", 1)
-    TC_D2 = _tc_mode("D2", 1)
+    # mode 2 (default): bf16 NHWC activations between layers, TMA-fed tcgen05 kernel (csrc/conv_tma.cu)
+    TC_D1 = _tc_mode("D1", 2)
+    TC_ENH = _tc_mode("ENH", 2)
+    TC_D2 = _tc_mode("D2", 2)
 
     def __init__(self, model):
         self.model = model
@@ -304,10 +305,20 @@ class FrameEngine:
         """L2 = clamp((x+eps) - denoise_1(x+eps), eps, 1)   (model.py:313-316).  `tag` names a private set of
         activation buffers (training keeps them for the backward pass)."""
         w, ws, HW = self.w, self.ws, H * W
+        d = ws.get("d4" + tag, (HW, 4))
+        if self.TC_D1 == 2:
+            bf = torch.bfloat16
+            xp, a1, a2 = ws.get("xp8", (HW, 8), bf), ws.get("b48a", (HW, 48), bf), ws.get("b48b", (HW, 48), bf)
+            ops.pack_nhwc_bf16([x], 3, self.EPS, xp, 8, HW)
+            ops.conv2d_bf16(w["d1.c1"], xp, 8, H, W, a1, 48, act="lrelu")
+            ops.conv2d_bf16(w["d1.c2"], a1, 48, H, W, a2, 48, act="lrelu")
+            ops.conv2d_bf16(w["d1.c3"], a2, 48, H, W, d, 4, out_f32=True)
+            L2 = torch.empty_like(x)
+            ops.retinex_l2(x, d, 4, L2, HW, self.EPS)
+            return L2
         xp = ws.get("xp" + tag, (HW, 4))
         a1 = ws.get("a48a" + tag, (HW, 48))
         a2 = ws.get("a48b" + tag, (HW, 48))
-        d = ws.get("d4" + tag, (HW, 4))
         ops.pack_nhwc([x], 3, self.EPS, xp, 4, HW)
         ops.conv2d(w["d1.c1"], xp, 4, 4, 1, H, W, a1, 48, pad=(1, 1), act="lrelu", tc=self.TC_D1)
         ops.conv2d(w["d1.c2"], a1, 48, 48, 1, H, W, a2, 48, pad=(1, 1), act="lrelu", tc=self.TC_D1)
@@ -319,10 +330,23 @@ class FrameEngine:
     def enhance_H2(self, x, H3_wp, s3_wp, L2, H, W):
         """s2 = enhance(cat[H3_wp, s3_wp, L2]); H2 = clamp((x+eps)/s2, eps, 1)  (model.py:326-328)."""
         w, ws, HW = self.w, self.ws, H * W
+        s4 = ws.get("s4", (HW, 4))
+        if self.TC_ENH == 2:
+            bf = torch.bfloat16
+            ep, cur, nxt = ws.get("ep16", (HW, 16), bf), ws.get("b64a", (HW, 64), bf), ws.get("b64b", (HW, 64), bf)
+            ops.pack_nhwc_bf16([H3_wp, s3_wp, L2], 3, 0.0, ep, 16, HW)
+            ops.conv2d_bf16(w["e.in"], ep, 16, H, W, cur, 64, act="relu")
+            for _ in range(3):  # one shared conv+BN applied three times (model.py:60-67, Q5)
+                ops.conv2d_bf16(w["e.blk"], cur, 64, H, W, nxt, 64, act="relu", res=cur, res_cs=64)
+                cur, nxt = nxt, cur
+            ops.conv2d_bf16(w["e.out"], cur, 64, H, W, s4, 4, act="sigmoid", out_f32=True)
+            s2 = torch.empty_like(x)
+            H2 = torch.empty_like(x)
+            ops.retinex_h2(x, s4, 4, s2, H2, HW, self.EPS)
+            return s2, H2
         ep = ws.get("ep12", (HW, 12))
         fa = ws.get("f64a", (HW, 64))
         fb = ws.get("f64b", (HW, 64))
-        s4 = ws.get("s4", (HW, 4))
         ops.pack_nhwc([H3_wp, s3_wp, L2], 3, 0.0, ep, 12, HW)
         ops.conv2d(w["e.in"], ep, 12, 12, 1, H, W, fa, 64, pad=(1, 1), act="relu", tc=self.TC_ENH)
         cur, nxt = fa, fb
@@ -339,10 +363,21 @@ class FrameEngine:
     def denoise2_H3(self, H3_wp, s3_wp, H2, s2, H, W, tag=""):
         """H5 = clamp(cat[H2,s2] - denoise_2(cat[H3_wp,s3_wp,H2,s2]), eps, 1)  (model.py:334-337)."""
         w, ws, HW = self.w, self.ws, H * W
+        d = ws.get("d8" + tag, (HW, 8))
+        if self.TC_D2 == 2:
+            bf = torch.bfloat16
+            dp, a1, a2 = ws.get("dp16", (HW, 16), bf), ws.get("b48a", (HW, 48), bf), ws.get("b48b", (HW, 48), bf)
+            ops.pack_nhwc_bf16([H3_wp, s3_wp, H2, s2], 3, 0.0, dp, 16, HW)
+            ops.conv2d_bf16(w["d2.c1"], dp, 16, H, W, a1, 48, act="lrelu")
+            ops.conv2d_bf16(w["d2.c2"], a1, 48, H, W, a2, 48, act="lrelu")
+            ops.conv2d_bf16(w["d2.c3"], a2, 48, H, W, d, 8, out_f32=True)
+            H3 = torch.empty_like(H2)
+            s3 = torch.empty_like(H2)
+            ops.retinex_h5(H2, s2, d, 8, H3, s3, HW, self.EPS)
+            return H3, s3
         dp = ws.get("dp12" + tag, (HW, 12))
         a1 = ws.get("a48a" + tag, (HW, 48))
         a2 = ws.get("a48b" + tag, (HW, 48))
-        d = ws.get("d8" + tag, (HW, 8))
         ops.pack_nhwc([H3_wp, s3_wp, H2, s2], 3, 0.0, dp, 12, HW)
         ops.conv2d(w["d2.c1"], dp, 12, 12, 1, H, W, a1, 48, pad=(1, 1), act="lrelu", tc=self.TC_D2)
         ops.conv2d(w["d2.c2"], a1, 48, 48, 1, H, W, a2, 48, pad=(1, 1), act="lrelu", tc=self.TC_D2)

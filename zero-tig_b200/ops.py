@@ -9,7 +9,7 @@ import ctypes as C
 import torch
 
 from . import _lib
-from ._lib import ZtConv, check, lib
+from ._lib import ZtConv, ZtConvBf16, check, lib
 
 ACT = {"none": 0, "relu": 1, "lrelu": 2, "sigmoid": 3, "tanh": 4}
 EPI = {"plain": 0, "gru_zr": 1, "gru_q": 2, "add_relu": 3, "add": 4}
@@ -30,7 +30,7 @@ def _p(t, offset_elems=0):
 
 class ConvW:
     """A conv layer's parameters in kernel layout: weight [kh][kw][cin_pad][w_cs], bias [cout]."""
-    __slots__ = ("w", "b", "kh", "kw", "cin", "cout", "w_cs", "w_raw", "_tc")
+    __slots__ = ("w", "b", "kh", "kw", "cin", "cout", "w_cs", "w_raw", "b_raw", "_tc")
 
     def __init__(self, weight, bias=None, cin_pad=None, bn=None, eps=1e-5, out_slice=None):
         w = weight.detach().float()
@@ -52,6 +52,7 @@ class ConvW:
         self.w, self.b = wk.contiguous(), (None if b is None else b.contiguous())
         self.kh, self.kw, self.cin, self.cout, self.w_cs = kh, kw, cin_p, cout, w_cs
         self.w_raw, self._tc = w, {}
+        self.b_raw = b
 
     def tc_pack(self, BN):
         """bf16 hi/lo weights in the tcgen05 kernel's layout (csrc/conv_tc.cu):
@@ -76,6 +77,42 @@ class ConvW:
             t = torch.gather(x, 5, idx).contiguous()
             self._tc[BN] = t
         return t
+
+
+    def tma_pack(self):
+        """bf16 weights for csrc/conv_tma.cu: [tap][BN = ceil16(cout)][64 ch] rows of 128 B, 16 B chunk j of
+        row n stored at chunk position j ^ (n & 7) (UMMA / TMA 128-byte swizzle); cin, cout zero padded."""
+        t = self._tc.get("tma")
+        if t is None:
+            w = self.w_raw
+            cout, cin, kh, kw = w.shape
+            assert cin <= 64 and cout <= 64
+            BN = (cout + 15) // 16 * 16
+            wp = torch.zeros(BN, 64, kh, kw, device=w.device, dtype=torch.float32)
+            wp[:cout, :cin] = w
+            x = wp.to(torch.bfloat16).permute(2, 3, 0, 1).reshape(kh * kw, BN, 8, 8)   # tap, row, chunk, e
+            n = torch.arange(BN, device=w.device)
+            src = torch.arange(8, device=w.device)[None, :] ^ (n[:, None] & 7)
+            t = torch.gather(x, 2, src.view(1, BN, 8, 1).expand_as(x)).contiguous()
+            self._tc["tma"] = t
+        return t
+
+
+def conv2d_bf16(wt: ConvW, x, cin, H, W, out, out_cs, *, act="none", res=None, res_cs=0, out_f32=False):
+    """TMA-fed tcgen05 convolution over bf16 NHWC activations (csrc/conv_tma.cu): 3x3 pad 1 or 1x1."""
+    d = ZtConvBf16()
+    d.in_, d.cin = _p(x), cin
+    d.weight, d.bias = _p(wt.tma_pack()), _p(wt.b_raw)
+    d.out, d.out_cs, d.out_f32 = _p(out), out_cs, int(out_f32)
+    d.res, d.res_cs = _p(res), res_cs
+    d.H, d.W, d.cout, d.kh, d.kw, d.act = H, W, wt.w_raw.shape[0], wt.kh, wt.kw, ACT[act]
+    check(lib().zt_conv2d_bf16_tma(C.byref(d), _stream()), "conv2d_bf16_tma")
+
+
+def pack_nhwc_bf16(srcs, c_each, add, out, cs, HW):
+    s = list(srcs) + [None] * (4 - len(srcs))
+    check(lib().zt_pack_nhwc_bf16(_p(s[0]), _p(s[1]), _p(s[2]), _p(s[3]), c_each, len(srcs), add, _p(out), cs, HW,
+                                  _stream()), "pack_nhwc_bf16")
 
 
 def conv2d(wt: ConvW, in0, in0_cs, c0, B, H, W, out, out_cs, *, in0_off=0, in1=None, in1_cs=0, c1=0,
