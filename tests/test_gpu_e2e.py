@@ -117,3 +117,31 @@ def test_too_small_frame_is_refused(model_factory):
     m.is_new_seq = False
     with pytest.raises(RuntimeError, match="too small|NaN"):
         m(x)
+
+
+@pytest.mark.parametrize("u8", [False, True])
+def test_frame_pipeline_matches_direct_calls(model_factory, u8):
+    """FramePipeline (pinned host frames in, host H2/H3 out, copies on side streams) returns, in order, exactly
+    what per-frame model calls return; the u8 variant equals predict.py:57-61's clip(x*255).astype(uint8)."""
+    from zero_tig_b200 import synth
+    from zero_tig_b200.pipeline import FramePipeline
+    H, W, n = 128, 160, 7
+    clip = synth.synthetic_clip(n, H, W, seed=11)
+    a, b = model_factory(1), model_factory(1)
+    want = []
+    for t in range(n):
+        a.is_new_seq = (t == 0)
+        H2, H3, _ = a(clip[t:t + 1].cuda())
+        want.append((H2.cpu(), H3.cpu()))
+    got = {}
+    pipe = FramePipeline(b, H, W, depth=2, quantize_u8=u8)
+    frames = [clip[t:t + 1].pin_memory() for t in range(n)]
+    pipe.run(frames, lambda i, h2, h3: got.__setitem__(i, (h2.clone(), h3.clone())))
+    assert sorted(got) == list(range(n))
+    for t in range(n):
+        for g_, w_ in zip(got[t], want[t]):
+            if u8:
+                ref = np.clip(w_[0].numpy().transpose(1, 2, 0) * 255.0, 0, 255.0).astype("uint8")
+                assert g_.shape == (H, W, 3) and np.array_equal(g_.numpy(), ref), t
+            else:
+                assert torch.equal(g_, w_), t

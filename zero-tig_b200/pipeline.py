@@ -1,0 +1,74 @@
+"""Host-buffer frame pipeline around ``Finetunemodel`` (the loop of predict.py:76-89 with the copies overlapped).
+
+predict.py moves one frame to the GPU, runs the model, and copies ``H2`` / ``H3`` back for ``save_images``
+(predict.py:57-61,86-104), all on one stream.  ``FramePipeline`` keeps that contract - host frames in, host
+``(H2, H3)`` out, strictly in frame order, the recurrent state carried by the model - but runs the host->device
+copy of frame t+1 and the device->host copy of frame t-1 on two side streams while frame t computes.  No
+arithmetic happens here: only ``cudaMemcpyAsync`` on pinned buffers and stream events.
+"""
+import torch
+
+
+class FramePipeline:
+    def __init__(self, model, H, W, depth=2, quantize_u8=False):
+        if not torch.cuda.is_available():
+            raise RuntimeError("FramePipeline needs a CUDA device (no CPU fallback)")
+        self.model, self.H, self.W, self.depth = model, H, W, depth
+        self.dev = next(model.parameters()).device
+        self.quantize_u8 = quantize_u8
+        self.h2d, self.d2h = torch.cuda.Stream(self.dev), torch.cuda.Stream(self.dev)
+        self.dev_in = [torch.empty(1, 3, H, W, device=self.dev) for _ in range(depth)]
+        odt, oshape = (torch.uint8, (H, W, 3)) if quantize_u8 else (torch.float32, (1, 3, H, W))
+        self.host_out = [[torch.empty(oshape, dtype=odt).pin_memory() for _ in range(2)] for _ in range(depth)]
+        self.ev_in = [torch.cuda.Event() for _ in range(depth)]      # H2D of slot done
+        self.ev_free = [torch.cuda.Event() for _ in range(depth)]    # compute finished reading slot
+        self.ev_out = [torch.cuda.Event() for _ in range(depth)]     # D2H of slot done
+        self.h2d_bytes = 3 * H * W * 4
+        self.d2h_bytes = 2 * 3 * H * W * (1 if quantize_u8 else 4)
+
+    def _upload(self, slot, frame_host, first_use):
+        with torch.cuda.stream(self.h2d):
+            if not first_use:
+                self.h2d.wait_event(self.ev_free[slot])
+            self.dev_in[slot].copy_(frame_host, non_blocking=True)
+            self.ev_in[slot].record(self.h2d)
+
+    def run(self, frames, emit, new_sequence=True):
+        """frames: sequence of pinned host tensors [1,3,H,W] fp32 (one sequence, in order).
+        emit(i, H2_host, H3_host) is called in order once frame i's outputs are in host memory; the host
+        buffers are reused ``depth`` frames later."""
+        from . import ops
+        n = len(frames)
+        if n == 0:
+            return
+        cur = torch.cuda.current_stream(self.dev)
+        keep = [None] * self.depth
+        self._upload(0, frames[0], True)
+        for i in range(n):
+            slot = i % self.depth
+            if i + 1 < n:
+                self._upload((i + 1) % self.depth, frames[i + 1], i + 1 < self.depth)
+            cur.wait_event(self.ev_in[slot])
+            self.model.is_new_seq = bool(new_sequence and i == 0)
+            H2, H3, _ = self.model(self.dev_in[slot])
+            self.ev_free[slot].record(cur)
+            if i >= self.depth:                      # host/out slot about to be overwritten: hand it out first
+                self.ev_out[slot].synchronize()
+                emit(i - self.depth, *self.host_out[slot])
+            if self.quantize_u8:
+                q = [torch.empty(self.H, self.W, 3, dtype=torch.uint8, device=self.dev) for _ in range(2)]
+                ops.quantize_u8_hwc(H2, q[0], 3, self.H * self.W)
+                ops.quantize_u8_hwc(H3, q[1], 3, self.H * self.W)
+                H2, H3 = q
+            done = torch.cuda.Event()
+            done.record(cur)
+            with torch.cuda.stream(self.d2h):
+                self.d2h.wait_event(done)
+                self.host_out[slot][0].copy_(H2, non_blocking=True)
+                self.host_out[slot][1].copy_(H3, non_blocking=True)
+                self.ev_out[slot].record(self.d2h)
+            keep[slot] = (H2, H3)                    # keep the device tensors alive until their D2H completes
+        for i in range(max(0, n - self.depth), n):
+            slot = i % self.depth
+            self.ev_out[slot].synchronize()
+            emit(i, *self.host_out[slot])
