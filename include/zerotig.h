@@ -171,6 +171,17 @@ int zt_conv2d_bf16_tma(const ZtConvBf16* desc, void* stream);
 int zt_pack_nhwc_bf16(const float* s0, const float* s1, const float* s2, const float* s3, int c_each, int nsrc,
                       float add, void* out, int cs, int64_t HW, void* stream);
 
+/* ---- RAFT helpers around the tensor-core convolution ----
+ * [B][H][W][C] -> [B][H/2][W/2][4C] (channel = (by*2+bx)*C + c): lets the encoders' stride-2 convolutions
+ * (model/RAFT/extractor.py:44-48,131) run as stride-1 tensor-core convolutions with rearranged weights */
+int zt_space_to_depth2_f32(const float* in, int in_cs, int C, int B, int H, int W, float* out, void* stream);
+/* BasicMotionEncoder.convf1 + ReLU (model/RAFT/update.py:84,92): 7x7, 2 -> 128; weight fp32 [7][7][2][128] */
+int zt_raft_convf1_f32(const float* flow, int f_cs, const float* weight, const float* bias, float* out, int out_cs,
+                       int H, int W, void* stream);
+/* FlowHead.conv2 (model/RAFT/update.py:13-14): 3x3, C -> 2, no activation; weight fp32 [9][C][2] */
+int zt_conv3x3_n2_f32(const float* in, int in_cs, int C, const float* weight, const float* bias, float* out,
+                      int out_cs, int H, int W, void* stream);
+
 /* ---- training path: Network.forward (model/model.py:144-203) and loss.py -------------------
  * NCHW fp32, batch 1.  Reduction entry points ADD raw sums into fp64 accumulators the caller
  * zeroes; the host turns them into the 17 weighted terms of LossFunction.forward. */

@@ -326,3 +326,59 @@ def test_retinex_elementwise_and_quantize(dev):
     ops.quantize_u8_hwc(H2, u8, 3, HW)
     ref = np.clip(H2[0].permute(1, 2, 0).cpu().numpy() * 255, 0, 255).astype(np.uint8)   # predict.py:57-61
     assert np.array_equal(u8.cpu().numpy(), ref)
+
+
+@pytest.mark.parametrize("cin,cout,k,pad,B,H,W", [(4, 64, 7, 3, 2, 40, 56), (64, 96, 3, 1, 1, 24, 40),
+                                                   (96, 128, 3, 1, 2, 16, 24)])
+def test_stride2_conv_via_space_to_depth(cin, cout, k, pad, B, H, W):
+    """A stride-2 convolution (extractor.py:44-48,131) equals the stride-1 tensor-core convolution over the
+    space-to-depth input with ops.s2d_weight's rearranged kernel (cropped to the reference output size)."""
+    import torch.nn.functional as F
+    from zero_tig_b200 import ops
+    g = torch.Generator().manual_seed(cin + cout)
+    x = torch.randn(B, cin, H, W, generator=g).cuda()
+    w = (torch.randn(cout, cin, k, k, generator=g) * (1.0 / (cin * k * k) ** 0.5)).cuda()
+    b = (torch.randn(cout, generator=g) * 0.1).cuda()
+    ref = F.conv2d(x, w, b, stride=2, padding=pad)
+    ho, wo = ref.shape[-2:]
+    assert (ho, wo) == (H // 2, W // 2)
+    xn = x.permute(0, 2, 3, 1).reshape(B * H * W, cin).contiguous()
+    xs = torch.empty(B * ho * wo, 4 * cin, device="cuda")
+    ops.space_to_depth2(xn, cin, cin, B, H, W, xs)
+    ws, npad = ops.s2d_weight(w, pad)
+    wt = ops.ConvW(ws, b)
+    out = torch.empty(B * ho * wo, cout, device="cuda")
+    ops.conv2d(wt, xs, 4 * cin, 4 * cin, B, ho, wo, out, cout, pad=(npad, npad), tc=3, bn=64, crop=(ho, wo))
+    want = ref.permute(0, 2, 3, 1).reshape(B * ho * wo, cout)
+    assert (out - want).abs().max().item() < 2e-4 * max(1.0, want.abs().max().item())
+    # the 1x1 stride-2 shortcut = 1x1 convolution on block (0,0) of the space-to-depth tensor
+    w1 = (torch.randn(cout, cin, 1, 1, generator=g) * 0.1).cuda()
+    ref1 = F.conv2d(x, w1, None, stride=2).permute(0, 2, 3, 1).reshape(B * ho * wo, cout)
+    if cin % 64 == 0 or cin == 96:
+        ops.conv2d(ops.ConvW(w1), xs, 4 * cin, cin, B, ho, wo, out, cout, tc=3, bn=64)
+        assert (out - ref1).abs().max().item() < 2e-4 * max(1.0, ref1.abs().max().item())
+
+
+def test_raft_small_kernels_vs_torch():
+    """convf1 (7x7, 2->128, ReLU) and the flow head's 3x3 256->2 on the CUDA cores against torch conv2d."""
+    import torch.nn.functional as F
+    from zero_tig_b200 import ops
+    g = torch.Generator().manual_seed(21)
+    H, W = 23, 40
+    flow = torch.randn(1, 2, H, W, generator=g).cuda() * 3
+    w = (torch.randn(128, 2, 7, 7, generator=g) * 0.1).cuda()
+    b = (torch.randn(128, generator=g) * 0.1).cuda()
+    ref = torch.relu(F.conv2d(flow, w, b, padding=3))[0].permute(1, 2, 0).reshape(H * W, 128)
+    f4 = torch.zeros(H * W, 4, device="cuda")
+    f4[:, :2] = flow[0].permute(1, 2, 0).reshape(H * W, 2)
+    out = torch.empty(H * W, 128, device="cuda")
+    ops.raft_convf1(f4, 4, w.permute(2, 3, 1, 0).contiguous(), b, out, 128, H, W)
+    assert (out - ref).abs().max().item() < 1e-4
+    x = torch.randn(1, 256, H, W, generator=g).cuda()
+    w2 = (torch.randn(2, 256, 3, 3, generator=g) * 0.05).cuda()
+    b2 = torch.randn(2, generator=g).cuda()
+    ref2 = F.conv2d(x, w2, b2, padding=1)[0].permute(1, 2, 0).reshape(H * W, 2)
+    xn = x[0].permute(1, 2, 0).reshape(H * W, 256).contiguous()
+    d = torch.zeros(H * W, 4, device="cuda")
+    ops.conv3x3_n2(xn, 256, 256, w2.permute(2, 3, 1, 0).reshape(9, 256, 2).contiguous(), b2, d, 4, H, W)
+    assert (d[:, :2] - ref2).abs().max().item() < 1e-4 and torch.all(d[:, 2:] == 0)

@@ -47,6 +47,9 @@ SIGNATURES = {
     "zt_debug_set_tc_trace": [P, I],
     "zt_conv2d_bf16_tma": [C.POINTER(ZtConvBf16), P],
     "zt_pack_nhwc_bf16": [P, P, P, P, I, I, F, P, I, L, P],
+    "zt_space_to_depth2_f32": [P, I, I, I, I, I, P, P],
+    "zt_raft_convf1_f32": [P, I, P, P, P, I, I, I, P],
+    "zt_conv3x3_n2_f32": [P, I, I, P, P, P, I, I, I, P],
     "zt_pack_tc_rows_f32": [P, I, I, I, I, P, P],
     "zt_instnorm_nhwc_f32": [P, I, P, I, P, I, P, I, I, I, F, I, I, P],
     "zt_transpose_f32": [P, I, I, I, P, I, P],

@@ -577,7 +577,9 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
   ZT_REQUIRE(((uintptr_t)d.in0 & 15) == 0 && ((uintptr_t)d.weight & 15) == 0 && (d.c1 == 0 || ((uintptr_t)d.in1 & 15) == 0),
              "conv_tc: pointers must be 16-byte aligned");
   ZT_REQUIRE(d.B > 0 && d.H > 0 && d.W > 0 && d.cout > 0 && d.kh >= 1 && d.kw >= 1 && d.kh <= 7 && d.kw <= 7, "conv_tc: bad dims");
-  ZT_REQUIRE(d.Ho == d.H + 2 * d.ph - d.kh + 1 && d.Wo == d.W + 2 * d.pw - d.kw + 1 && d.Ho > 0 && d.Wo > 0,
+  // Ho/Wo may be cropped below the full correlation size (even kernels from the stride-2 -> stride-1
+  // space-to-depth rewrite produce one extra row/column that the reference convolution does not have)
+  ZT_REQUIRE(d.Ho <= d.H + 2 * d.ph - d.kh + 1 && d.Wo <= d.W + 2 * d.pw - d.kw + 1 && d.Ho > 0 && d.Wo > 0,
              "conv_tc: output dims inconsistent");
   if (d.epi == ZT_EPI_GRU_ZR) ZT_REQUIRE(d.aux0 && d.aux1 && (d.cout & 7) == 0, "conv_tc: GRU_ZR needs aux0/aux1 and cout%%8==0");
   if (d.epi == ZT_EPI_GRU_Q) ZT_REQUIRE(d.aux0 && d.aux1, "conv_tc: GRU_Q needs aux0/aux1");

@@ -72,9 +72,14 @@ class RaftEngine:
             return (sd[prefix + ".weight"], sd[prefix + ".bias"], sd[prefix + ".running_mean"],
                     sd[prefix + ".running_var"])
 
+        import torch.nn.functional as F
         for enc, is_bn in (("fnet", False), ("cnet", True)):
             w[f"{enc}.conv1"] = ConvW(sd[f"{enc}.conv1.weight"], sd[f"{enc}.conv1.bias"], cin_pad=4,
                                       bn=bn(f"{enc}.norm1") if is_bn else None)
+            # stride-2 convolutions as stride-1 convolutions over the space-to-depth input (tensor-core path)
+            w4 = F.pad(sd[f"{enc}.conv1.weight"], (0, 0, 0, 0, 0, 1))
+            w[f"{enc}.conv1.s2d"] = ConvW(ops.s2d_weight(w4, 3)[0], sd[f"{enc}.conv1.bias"],
+                                          bn=bn(f"{enc}.norm1") if is_bn else None)
             for li in (1, 2, 3):
                 for bi in (0, 1):
                     p = f"{enc}.layer{li}.{bi}"
@@ -83,6 +88,8 @@ class RaftEngine:
                     w[p + ".conv2"] = ConvW(sd[p + ".conv2.weight"], sd[p + ".conv2.bias"],
                                             bn=bn(p + ".norm2") if is_bn else None)
                     if p + ".downsample.0.weight" in sd:
+                        w[p + ".conv1.s2d"] = ConvW(ops.s2d_weight(sd[p + ".conv1.weight"], 1)[0], sd[p + ".conv1.bias"],
+                                                    bn=bn(p + ".norm1") if is_bn else None)
                         w[p + ".down"] = ConvW(sd[p + ".downsample.0.weight"], sd[p + ".downsample.0.bias"],
                                                bn=bn(p + ".norm3") if is_bn else None)
         w["fnet.conv2"] = ConvW(sd["fnet.conv2.weight"], sd["fnet.conv2.bias"])
@@ -97,6 +104,11 @@ class RaftEngine:
             bz, br = sd[u + f"gru.convz{s}.bias"], sd[u + f"gru.convr{s}.bias"]
             w["gru.zr" + s] = ConvW(torch.cat([wz, wr], 0), torch.cat([bz, br], 0))
             w["gru.q" + s] = ConvW(sd[u + f"gru.convq{s}.weight"], sd[u + f"gru.convq{s}.bias"])
+        # CUDA-core fp32 kernels for the two degenerate GEMMs (K = 98 and N = 2)
+        w["enc.convf1.raw"] = (sd[u + "encoder.convf1.weight"].float().permute(2, 3, 1, 0).contiguous(),
+                               sd[u + "encoder.convf1.bias"].float().contiguous())
+        w["fh2.raw"] = (sd[u + "flow_head.conv2.weight"].float().permute(2, 3, 1, 0).reshape(9, 256, 2).contiguous(),
+                        sd[u + "flow_head.conv2.bias"].float().contiguous())
         w["fh1"] = ConvW(sd[u + "flow_head.conv1.weight"], sd[u + "flow_head.conv1.bias"])
         w["fh2"] = ConvW(sd[u + "flow_head.conv2.weight"], sd[u + "flow_head.conv2.bias"])
         w["mask0"] = ConvW(sd[u + "mask.0.weight"], sd[u + "mask.0.bias"])
@@ -115,7 +127,15 @@ class RaftEngine:
             return ws.get(f"{enc}.{tag}", (B * hh * ww, c))
 
         y = buf("stem", h, wd, 64)
-        ops.conv2d(w[enc + ".conv1"], x, 4, 4, B, H, W, y, 64, stride=2, pad=(3, 3), act="relu" if is_bn else "none")
+        s2d = bool(T) and H % 8 == 0 and W % 8 == 0
+        if s2d:
+            xs = buf("stem.s2d", h, wd, 16)
+            ops.space_to_depth2(x, 4, 4, B, H, W, xs)
+            ops.conv2d(w[enc + ".conv1.s2d"], xs, 16, 16, B, h, wd, y, 64, pad=(2, 2), act="relu" if is_bn else "none",
+                       tc=T, bn=64, crop=(h, wd))
+        else:
+            ops.conv2d(w[enc + ".conv1"], x, 4, 4, B, H, W, y, 64, stride=2, pad=(3, 3),
+                       act="relu" if is_bn else "none")
         if not is_bn:
             ops.instnorm(y, 64, y, 64, stats, B, h * wd, 64, relu_inner=True)
         cin = 64
@@ -125,14 +145,24 @@ class RaftEngine:
                 p = f"{enc}.layer{li}.{bi}"
                 ho, wo = h // s if s == 1 else (h + 2 - 3) // s + 1, wd // s if s == 1 else (wd + 2 - 3) // s + 1
                 t1 = buf(f"l{li}b{bi}.t1", ho, wo, cout)
-                ops.conv2d(w[p + ".conv1"], y, cin, cin, B, h, wd, t1, cout, stride=s, pad=(1, 1),
-                           act="relu" if is_bn else "none", tc=T if s == 1 else 0, bn=64)
+                ys = None
+                if s != 1 and s2d:
+                    ys = buf(f"l{li}.s2d", ho, wo, 4 * cin)
+                    ops.space_to_depth2(y, cin, cin, B, h, wd, ys)
+                    ops.conv2d(w[p + ".conv1.s2d"], ys, 4 * cin, 4 * cin, B, ho, wo, t1, cout, pad=(1, 1),
+                               act="relu" if is_bn else "none", tc=T, bn=64, crop=(ho, wo))
+                else:
+                    ops.conv2d(w[p + ".conv1"], y, cin, cin, B, h, wd, t1, cout, stride=s, pad=(1, 1),
+                               act="relu" if is_bn else "none", tc=T if s == 1 else 0, bn=64)
                 if not is_bn:
                     ops.instnorm(t1, cout, t1, cout, stats, B, ho * wo, cout, relu_inner=True)
                 sc = y
                 if s != 1:
                     sc = buf(f"l{li}b{bi}.sc", ho, wo, cout)
-                    ops.conv2d(w[p + ".down"], y, cin, cin, B, h, wd, sc, cout, stride=s, pad=(0, 0))
+                    if ys is not None:   # 1x1 stride 2 = 1x1 on block (0,0) of the space-to-depth tensor
+                        ops.conv2d(w[p + ".down"], ys, 4 * cin, cin, B, ho, wo, sc, cout, tc=T, bn=64)
+                    else:
+                        ops.conv2d(w[p + ".down"], y, cin, cin, B, h, wd, sc, cout, stride=s, pad=(0, 0))
                     if not is_bn:
                         ops.instnorm(sc, cout, sc, cout, stats, B, ho * wo, cout, relu_inner=False)
                 out = buf(f"l{li}b{bi}.out", ho, wo, cout)
@@ -218,7 +248,10 @@ class RaftEngine:
             ops.corr_lookup(lv, hs, wsz, coords1, corr, 324, N)
             ops.conv2d(w["enc.convc1"], corr, 324, 324, 1, h8, w8, c1, 256, act="relu", tc=T, bn=64)
             ops.conv2d(w["enc.convc2"], c1, 256, 256, 1, h8, w8, c2f, 256, pad=(1, 1), act="relu", tc=T, bn=64)
-            ops.conv2d(w["enc.convf1"], flow4, 4, 4, 1, h8, w8, f1, 128, pad=(3, 3), act="relu", tc=T, bn=64)
+            if T:
+                ops.raft_convf1(flow4, 4, w["enc.convf1.raw"][0], w["enc.convf1.raw"][1], f1, 128, h8, w8)
+            else:
+                ops.conv2d(w["enc.convf1"], flow4, 4, 4, 1, h8, w8, f1, 128, pad=(3, 3), act="relu", tc=T, bn=64)
             ops.conv2d(w["enc.convf2"], f1, 128, 128, 1, h8, w8, c2f, 256, out_off=192, pad=(1, 1), act="relu", tc=T, bn=32)
             ops.conv2d(w["enc.conv"], c2f, 256, 256, 1, h8, w8, hx, 384, out_off=256, pad=(1, 1), act="relu", tc=T, bn=64)
             for s, pad in (("1", (0, 2)), ("2", (2, 0))):
@@ -227,7 +260,10 @@ class RaftEngine:
                 ops.conv2d(w["gru.q" + s], rh, 128, 128, 1, h8, w8, hx, 384, in1=hx, in1_cs=384, c1=256,
                            in1_off=128, pad=pad, epi="gru_q", aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128, tc=T, bn=32)
             ops.conv2d(w["fh1"], hx, 384, 128, 1, h8, w8, fhid, 256, pad=(1, 1), act="relu", tc=TH, bn=64)
-            ops.conv2d(w["fh2"], fhid, 256, 256, 1, h8, w8, delta, 4, pad=(1, 1), tc=TH)
+            if TH:
+                ops.conv3x3_n2(fhid, 256, 256, w["fh2.raw"][0], w["fh2.raw"][1], delta, 4, h8, w8)
+            else:
+                ops.conv2d(w["fh2"], fhid, 256, 256, 1, h8, w8, delta, 4, pad=(1, 1), tc=TH)
             ops.flow_update(coords1, delta, 4, flow4, 4, hx, 384, 382, h8, w8)
         # convex upsampling mask only for the returned (last) prediction (raft.py:122-130, Q15)
         mh = ws.get("maskh", (N, 256))

@@ -117,13 +117,17 @@ def pack_nhwc_bf16(srcs, c_each, add, out, cs, HW):
 
 def conv2d(wt: ConvW, in0, in0_cs, c0, B, H, W, out, out_cs, *, in0_off=0, in1=None, in1_cs=0, c1=0,
            in1_off=0, out_off=0, stride=1, pad=(0, 0), act="none", scale=1.0, epi="plain",
-           aux0=None, aux0_cs=0, aux0_off=0, aux1=None, aux1_cs=0, aux1_off=0, tc=0, bn=None):
-    """out[:, out_off:out_off+cout] = epilogue(conv(cat[in0[:, in0_off:+c0], in1[:, in1_off:+c1]]))."""
+           aux0=None, aux0_cs=0, aux0_off=0, aux1=None, aux1_cs=0, aux1_off=0, tc=0, bn=None, crop=None):
+    """out[:, out_off:out_off+cout] = epilogue(conv(cat[in0[:, in0_off:+c0], in1[:, in1_off:+c1]])).
+    crop = (Ho, Wo) keeps only the top-left part of the output (tensor-core path; see s2d_weight)."""
     assert c0 + c1 == wt.cin, (c0, c1, wt.cin)
     sh = sw = stride
     ph, pw = pad
     Ho = (H + 2 * ph - wt.kh) // sh + 1
     Wo = (W + 2 * pw - wt.kw) // sw + 1
+    if crop is not None:
+        assert tc and crop[0] <= Ho and crop[1] <= Wo
+        Ho, Wo = crop
     d = ZtConv()
     d.in0, d.in0_cs, d.c0 = _p(in0, in0_off), in0_cs, c0
     d.in1, d.in1_cs, d.c1 = _p(in1, in1_off), in1_cs, c1
@@ -163,6 +167,35 @@ class RowsAsWeights:
     def tc_pack(self, BN):
         assert BN == self.BN
         return self.buf
+
+
+def s2d_weight(w, pad):
+    """Weights of the stride-1 convolution over the space-to-depth input that equals a stride-2 convolution
+    (square kernel k, padding `pad`): w [co][ci][k][k] -> ([co][4*ci][n][n], new_pad) with input row
+    2*(oy+a)+b <-> tap a, block row b (same for columns); taps without a source are zero."""
+    co, ci, k, _ = w.shape
+    amin, amax = (0 - pad) // 2, (k - 1 - pad) // 2
+    n = amax - amin + 1
+    out = torch.zeros(co, 4 * ci, n, n, device=w.device, dtype=w.dtype)
+    for ky in range(k):
+        ay, by = divmod(ky - pad, 2)
+        for kx in range(k):
+            ax, bx = divmod(kx - pad, 2)
+            blk = by * 2 + bx
+            out[:, blk * ci:(blk + 1) * ci, ay - amin, ax - amin] = w[:, :, ky, kx]
+    return out, -amin
+
+
+def space_to_depth2(x, x_cs, Cn, B, H, W, out):
+    check(lib().zt_space_to_depth2_f32(_p(x), x_cs, Cn, B, H, W, _p(out), _stream()), "space_to_depth2")
+
+
+def raft_convf1(flow, f_cs, w, b, out, out_cs, H, W):
+    check(lib().zt_raft_convf1_f32(_p(flow), f_cs, _p(w), _p(b), _p(out), out_cs, H, W, _stream()), "raft_convf1")
+
+
+def conv3x3_n2(x, x_cs, Cn, w, b, out, out_cs, H, W):
+    check(lib().zt_conv3x3_n2_f32(_p(x), x_cs, Cn, _p(w), _p(b), _p(out), out_cs, H, W, _stream()), "conv3x3_n2")
 
 
 def instnorm(x, x_cs, out, out_cs, stats, B, HW, Cn, relu_inner, relu_outer=False, res=None, res_cs=0, eps=1e-5):
