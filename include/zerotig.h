@@ -66,6 +66,9 @@ typedef struct ZtConv {
   int act; float out_scale; int epi;
   const float* aux0; int aux0_cs;
   float* aux1; int aux1_cs;
+  const float* bplane; int bplane_cs;   /* optional per-pixel bias [M][bplane_cs] added before the epilogue (tensor-core
+                                          path only): the iteration-invariant part of a GRU convolution, i.e. the
+                                          convolution of the context features `inp` (update.py:47,50), computed once per frame */
 } ZtConv;
 int zt_conv2d_nhwc_f32(const ZtConv* d, void* stream);
 

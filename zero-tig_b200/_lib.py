@@ -24,6 +24,7 @@ class ZtConv(C.Structure):
         ("act", C.c_int), ("out_scale", C.c_float), ("epi", C.c_int),
         ("aux0", c_fp), ("aux0_cs", C.c_int),
         ("aux1", c_fp), ("aux1_cs", C.c_int),
+        ("bplane", c_fp), ("bplane_cs", C.c_int),
     ]
 
 

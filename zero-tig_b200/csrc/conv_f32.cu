@@ -227,6 +227,7 @@ extern "C" int zt_conv2d_nhwc_f32(const ZtConv* dp, void* stream) {
   const ZtConv& d = *dp;
   const int cin = d.c0 + d.c1;
   ZT_REQUIRE(d.in0 && d.weight && d.out, "conv: null pointer");
+  ZT_REQUIRE(d.bplane == nullptr, "conv: the per-pixel bias plane is a tensor-core-path feature");
   ZT_REQUIRE((d.c0 & 3) == 0 && (d.c1 & 3) == 0 && cin > 0, "conv: channel counts must be multiples of 4 (c0=%d c1=%d)", d.c0, d.c1);
   ZT_REQUIRE((d.in0_cs & 3) == 0 && (d.c1 == 0 || ((d.in1_cs & 3) == 0 && d.in1)), "conv: input channel strides must be multiples of 4");
   ZT_REQUIRE((d.w_cs & 3) == 0 && d.w_cs >= d.cout, "conv: weight row stride %d must be a multiple of 4 and >= cout %d", d.w_cs, d.cout);

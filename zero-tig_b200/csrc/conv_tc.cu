@@ -232,9 +232,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
         const int nb = n0 + ch * 32 + piece * 4;          // this thread's 4 output channels
         const int nvalid = nend - nb;
         // residual / gate operands do not depend on the MMAs: fetch them before waiting
-        float4 a0[8], a1[8];
+        // (the GRU epilogues need h, z and the bias plane: 96 live registers next to the accumulator would
+        // spill, so those instances fetch their operands in two batches after the accumulator is staged)
+        constexpr bool GRU = (EPI_T == ZT_EPI_GRU_ZR || EPI_T == ZT_EPI_GRU_Q);
+        float4 a0[GRU ? 1 : 8], a1[GRU ? 1 : 8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
+        for (int k = 0; k < (GRU ? 0 : 8); ++k) {
           a0[k] = make_float4(0.f, 0.f, 0.f, 0.f);
           a1[k] = make_float4(0.f, 0.f, 0.f, 0.f);
           const bool okk = (oyb + (k >> 1) < d.Ho) && (oxb + 4 * (k & 1) < d.Wo) && nvalid > 0;
@@ -284,13 +287,49 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
             *reinterpret_cast<uint4*>(stage + lane * TC_EPI_LD + 16 + 4 * i) = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
         }
         __syncwarp();
+        if constexpr (GRU) {
+          // operands: h (aux0), z (aux1, GRU_Q only) and the optional per-frame bias plane (the
+          // iteration-invariant share of the convolution); 4 pixels per batch, all loads of a batch in flight
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const bool okk = (oyb + (k >> 1) < d.Ho) && (oxb + 4 * (k & 1) < d.Wo) && nvalid > 0;
-          if (okk) {
-            const float4 x = *reinterpret_cast<const float4*>(stage + (4 * k + rsub) * TC_EPI_LD + piece * 4);
-            const int64_t m = mb + (int64_t)(k >> 1) * d.Wo + 4 * (k & 1);
-            tc_epilogue4<EPI_T, ACT_T>(d, m, nb, nend, x.x, x.y, x.z, x.w, bv, a0[k], a1[k]);
+          for (int kb = 0; kb < 8; kb += 4) {
+            float4 h4[4], z4[4], b4[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int k = kb + j;
+              const bool okk = (oyb + (k >> 1) < d.Ho) && (oxb + 4 * (k & 1) < d.Wo) && nvalid > 0;
+              const int64_t m = mb + (int64_t)(k >> 1) * d.Wo + 4 * (k & 1);
+              h4[j] = z4[j] = b4[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (okk) {
+                if (EPI_T == ZT_EPI_GRU_ZR) {
+                  if (nb >= Ch) h4[j] = ld4_or_scalar(d.aux0 + m * d.aux0_cs + (nb - Ch), nvalid);
+                } else {
+                  h4[j] = ld4_or_scalar(d.aux0 + m * d.aux0_cs + nb, nvalid);
+                  z4[j] = ld4_or_scalar(d.aux1 + m * d.aux1_cs + nb, nvalid);
+                }
+                if (d.bplane) b4[j] = ld4_or_scalar(d.bplane + m * d.bplane_cs + nb, nvalid);
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int k = kb + j;
+              const bool okk = (oyb + (k >> 1) < d.Ho) && (oxb + 4 * (k & 1) < d.Wo) && nvalid > 0;
+              if (okk) {
+                const float4 x = *reinterpret_cast<const float4*>(stage + (4 * k + rsub) * TC_EPI_LD + piece * 4);
+                const int64_t m = mb + (int64_t)(k >> 1) * d.Wo + 4 * (k & 1);
+                tc_epilogue4<EPI_T, ACT_T>(d, m, nb, nend, x.x + b4[j].x, x.y + b4[j].y, x.z + b4[j].z, x.w + b4[j].w,
+                                           bv, h4[j], z4[j]);
+              }
+            }
+          }
+        } else {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const bool okk = (oyb + (k >> 1) < d.Ho) && (oxb + 4 * (k & 1) < d.Wo) && nvalid > 0;
+            if (okk) {
+              const float4 x = *reinterpret_cast<const float4*>(stage + (4 * k + rsub) * TC_EPI_LD + piece * 4);
+              const int64_t m = mb + (int64_t)(k >> 1) * d.Wo + 4 * (k & 1);
+              tc_epilogue4<EPI_T, ACT_T>(d, m, nb, nend, x.x, x.y, x.z, x.w, bv, a0[k], a1[k]);
+            }
           }
         }
         __syncwarp();
@@ -582,6 +621,7 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
   ZT_REQUIRE(d.Ho <= d.H + 2 * d.ph - d.kh + 1 && d.Wo <= d.W + 2 * d.pw - d.kw + 1 && d.Ho > 0 && d.Wo > 0,
              "conv_tc: output dims inconsistent");
   if (d.epi == ZT_EPI_GRU_ZR) ZT_REQUIRE(d.aux0 && d.aux1 && (d.cout & 7) == 0, "conv_tc: GRU_ZR needs aux0/aux1 and cout%%8==0");
+  ZT_REQUIRE(!d.bplane || d.epi == ZT_EPI_GRU_ZR || d.epi == ZT_EPI_GRU_Q, "conv_tc: the bias plane is wired for the GRU epilogues only");
   if (d.epi == ZT_EPI_GRU_Q) ZT_REQUIRE(d.aux0 && d.aux1, "conv_tc: GRU_Q needs aux0/aux1");
   if (d.epi == ZT_EPI_ADD_RELU || d.epi == ZT_EPI_ADD) ZT_REQUIRE(d.aux0, "conv_tc: residual epilogue needs aux0");
   ZT_REQUIRE((int64_t)d.B * d.H * d.W < (1ll << 31), "conv_tc: too many pixels");

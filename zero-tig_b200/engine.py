@@ -104,6 +104,14 @@ class RaftEngine:
             bz, br = sd[u + f"gru.convz{s}.bias"], sd[u + f"gru.convr{s}.bias"]
             w["gru.zr" + s] = ConvW(torch.cat([wz, wr], 0), torch.cat([bz, br], 0))
             w["gru.q" + s] = ConvW(sd[u + f"gru.convq{s}.weight"], sd[u + f"gru.convq{s}.bias"])
+            # the context features `inp` (input channels 128..255 of cat[h, inp, motion], update.py:130) do not
+            # change over the 12 iterations: their share of every GRU convolution (+ bias) is computed once per
+            # frame and enters the loop convolutions as a per-pixel bias plane; the loop runs on K = 256 channels
+            wzr, wq = torch.cat([wz, wr], 0), sd[u + f"gru.convq{s}.weight"]
+            w[f"gru.zr{s}.inp"] = ConvW(wzr[:, 128:256].contiguous(), torch.cat([bz, br], 0))
+            w[f"gru.q{s}.inp"] = ConvW(wq[:, 128:256].contiguous(), sd[u + f"gru.convq{s}.bias"])
+            w[f"gru.zr{s}.hm"] = ConvW(torch.cat([wzr[:, :128], wzr[:, 256:]], 1).contiguous(), None)
+            w[f"gru.q{s}.hm"] = ConvW(torch.cat([wq[:, :128], wq[:, 256:]], 1).contiguous(), None)
         # CUDA-core fp32 kernels for the two degenerate GEMMs (K = 98 and N = 2)
         w["enc.convf1.raw"] = (sd[u + "encoder.convf1.weight"].float().permute(2, 3, 1, 0).contiguous(),
                                sd[u + "encoder.convf1.bias"].float().contiguous())
@@ -244,6 +252,13 @@ class RaftEngine:
         delta = ws.get("delta", (N, 4), zero=True)
         ops.flow_update(coords1, None, 0, flow4, 4, hx, 384, 382, h8, w8)
         T = self.TC_UPD
+        gru_pre = {}
+        if T:
+            for s, pad in (("1", (0, 2)), ("2", (2, 0))):
+                for kind, co in (("zr", 256), ("q", 128)):
+                    P = ws.get(f"gru.pre.{kind}{s}", (N, co))
+                    ops.conv2d(w[f"gru.{kind}{s}.inp"], hx, 384, 128, 1, h8, w8, P, co, in0_off=128, pad=pad, tc=T, bn=64)
+                    gru_pre[kind + s] = P
         for it in range(iters):
             ops.corr_lookup(lv, hs, wsz, coords1, corr, 324, N)
             ops.conv2d(w["enc.convc1"], corr, 324, 324, 1, h8, w8, c1, 256, act="relu", tc=T, bn=64)
@@ -255,6 +270,14 @@ class RaftEngine:
             ops.conv2d(w["enc.convf2"], f1, 128, 128, 1, h8, w8, c2f, 256, out_off=192, pad=(1, 1), act="relu", tc=T, bn=32)
             ops.conv2d(w["enc.conv"], c2f, 256, 256, 1, h8, w8, hx, 384, out_off=256, pad=(1, 1), act="relu", tc=T, bn=64)
             for s, pad in (("1", (0, 2)), ("2", (2, 0))):
+                if T:
+                    ops.conv2d(w[f"gru.zr{s}.hm"], hx, 384, 128, 1, h8, w8, rh, 128, in1=hx, in1_cs=384, c1=128,
+                               in1_off=256, pad=pad, epi="gru_zr", aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128, tc=T,
+                               bn=64, bplane=gru_pre["zr" + s], bplane_cs=256)
+                    ops.conv2d(w[f"gru.q{s}.hm"], rh, 128, 128, 1, h8, w8, hx, 384, in1=hx, in1_cs=384, c1=128,
+                               in1_off=256, pad=pad, epi="gru_q", aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128, tc=T,
+                               bn=32, bplane=gru_pre["q" + s], bplane_cs=128)
+                    continue
                 ops.conv2d(w["gru.zr" + s], hx, 384, 384, 1, h8, w8, rh, 128, pad=pad, epi="gru_zr",
                            aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128, tc=T, bn=64)
                 ops.conv2d(w["gru.q" + s], rh, 128, 128, 1, h8, w8, hx, 384, in1=hx, in1_cs=384, c1=256,

@@ -117,7 +117,7 @@ def pack_nhwc_bf16(srcs, c_each, add, out, cs, HW):
 
 def conv2d(wt: ConvW, in0, in0_cs, c0, B, H, W, out, out_cs, *, in0_off=0, in1=None, in1_cs=0, c1=0,
            in1_off=0, out_off=0, stride=1, pad=(0, 0), act="none", scale=1.0, epi="plain",
-           aux0=None, aux0_cs=0, aux0_off=0, aux1=None, aux1_cs=0, aux1_off=0, tc=0, bn=None, crop=None):
+           aux0=None, aux0_cs=0, aux0_off=0, aux1=None, aux1_cs=0, aux1_off=0, tc=0, bn=None, crop=None, bplane=None, bplane_cs=0):
     """out[:, out_off:out_off+cout] = epilogue(conv(cat[in0[:, in0_off:+c0], in1[:, in1_off:+c1]])).
     crop = (Ho, Wo) keeps only the top-left part of the output (tensor-core path; see s2d_weight)."""
     assert c0 + c1 == wt.cin, (c0, c1, wt.cin)
@@ -139,6 +139,7 @@ def conv2d(wt: ConvW, in0, in0_cs, c0, B, H, W, out, out_cs, *, in0_off=0, in1=N
     d.act, d.out_scale, d.epi = ACT[act], scale, EPI[epi]
     d.aux0, d.aux0_cs = _p(aux0, aux0_off), aux0_cs
     d.aux1, d.aux1_cs = _p(aux1, aux1_off), aux1_cs
+    d.bplane, d.bplane_cs = _p(bplane), bplane_cs
     if tc:
         # tensor-core path: tc = 1 (bf16) or 3 (bf16 hi/lo split, 3 products ~ fp32-grade)
         BN = bn or min((wt.cout + 15) // 16 * 16, 128)
