@@ -130,10 +130,11 @@ __device__ __forceinline__ void tc_epilogue4(const ZtConv& d, int64_t m, int nb,
   for (int e = 0; e < 4; ++e) {
     float x = v[e] + b[e];
     if (epi == ZT_EPI_GRU_ZR) {
-      x = 1.f / (1.f + expf(-x));
+      x = __fdividef(1.f, 1.f + __expf(-x));            // ~1e-6 absolute: far inside the 0.01 px EPE gate
       if (nb >= Ch) x *= a0[e];
     } else if (epi == ZT_EPI_GRU_Q) {
-      x = (1.f - a1[e]) * a0[e] + a1[e] * tanhf(x);
+      const float th = 1.f - __fdividef(2.f, 1.f + __expf(2.f * x));   // tanh(x), saturates cleanly to +-1
+      x = (1.f - a1[e]) * a0[e] + a1[e] * th;
     } else if (epi == ZT_EPI_ADD_RELU) {
       x = fmaxf(a0[e] + act_t<ACT_T>(x, d.act) * d.out_scale, 0.f);
     } else if (epi == ZT_EPI_ADD) {
