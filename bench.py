@@ -97,7 +97,7 @@ WARP_BYTES = 2 * 360 * 640 * 4 + 4 * 3 * H * W * 4                      # flow +
 LOOKUP_BYTES_PER_ITER = 3600 * (324 * 4 + 4 * 100 * 4 + 8)
 # dram__bytes_read.sum + dram__bytes_write.sum of one full-resolution 64->64 conv_tc launch from the
 # committed `ncu --set full` capture (profiles/), or None until captured for the current kernel
-TRAFFIC_PER_LAUNCH = None
+TRAFFIC_PER_LAUNCH = 483.97e6   # enhancer block launch (64->64 + residual), profiles/r01_ncu_conv_tma_c64.txt
 
 
 def run_reference(args):
@@ -172,7 +172,9 @@ class OpTimer:
                     tag = "conv_frame"
                     cout, cin_r = wt.w_raw.shape[0], wt.w_raw.shape[1]
                     M = Hn * Wn
-                    byt = M * (2.0 * cin_s + (4.0 if k.get("out_f32") else 2.0) * ocs + (2.0 * cout if k.get("res") is not None else 0.0))
+                    res = k.get("res")
+                    res_b = 2.0 * cout if (res is not None and res.data_ptr() != a[1].data_ptr()) else 0.0   # residual == input: read once
+                    byt = M * (2.0 * cin_s + (4.0 if k.get("out_f32") else 2.0) * ocs + res_b)
                     self.bytes[tag] = self.bytes.get(tag, 0) + byt
                     self.flops[tag] = self.flops.get(tag, 0) + 2.0 * M * cout * cin_r * wt.kh * wt.kw
                 self.rec.setdefault(tag, []).append((e0, e1))

@@ -5,6 +5,7 @@
 // grid_sample's align_corners=False un-normalisation (quirks Q2, Q4, Q11 reproduced), then
 // gathers both images with the same coordinates.  HBM-bound: algorithmic bytes per pair =
 // flow + 2 images read + 2 images written.
+#include <stdlib.h>
 #include <algorithm>
 #include "common.cuh"
 
@@ -117,14 +118,18 @@ extern "C" int zt_warp_pair_f32(const float* flow, int hf, int wf, const float* 
   ZT_REQUIRE(flow && img_a && out_a && (!img_b || out_b), "warp_pair: null pointer");
   ZT_REQUIRE(C >= 1 && C <= 3 && H > 1 && W > 1 && hf > 0 && wf > 0, "warp_pair: bad dims (C=%d H=%d W=%d)", C, H, W);
   cudaStream_t st = (cudaStream_t)stream;
-  const bool vec = (W & 3) == 0 && ((uintptr_t)out_a & 15) == 0 && (!out_b || ((uintptr_t)out_b & 15) == 0);
+  // one pixel per thread: the gathers of a warp then cover contiguous rows (measured 77 us vs 105 us for the
+  // 4-pixels-per-thread mapping at 1080p, cold L2); ZT_WARP_VEC4=1 re-enables the vectorised-store variant
+  static const bool force_vec = getenv("ZT_WARP_VEC4") != nullptr;
+  static const int cap = getenv("ZT_WARP_CAP") ? atoi(getenv("ZT_WARP_CAP")) : 64;
+  const bool vec = force_vec && (W & 3) == 0 && ((uintptr_t)out_a & 15) == 0 && (!out_b || ((uintptr_t)out_b & 15) == 0);
   if (vec) {
     const int64_t total = (int64_t)H * (W / 4);
     const int blocks = (int)std::min<int64_t>(ceil_div64(total, 256), 16 * kNumSMs);
     warp_pair_kernel<4><<<blocks, 256, 0, st>>>(flow, hf, wf, img_a, img_b, out_a, out_b, C, H, W);
   } else {
     const int64_t total = (int64_t)H * W;
-    const int blocks = (int)std::min<int64_t>(ceil_div64(total, 256), 16 * kNumSMs);
+    const int blocks = (int)std::min<int64_t>(ceil_div64(total, 256), (int64_t)cap * kNumSMs);
     warp_pair_kernel<1><<<blocks, 256, 0, st>>>(flow, hf, wf, img_a, img_b, out_a, out_b, C, H, W);
   }
   return check_launch("warp_pair_kernel");
