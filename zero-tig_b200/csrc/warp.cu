@@ -118,11 +118,12 @@ extern "C" int zt_warp_pair_f32(const float* flow, int hf, int wf, const float* 
   ZT_REQUIRE(flow && img_a && out_a && (!img_b || out_b), "warp_pair: null pointer");
   ZT_REQUIRE(C >= 1 && C <= 3 && H > 1 && W > 1 && hf > 0 && wf > 0, "warp_pair: bad dims (C=%d H=%d W=%d)", C, H, W);
   cudaStream_t st = (cudaStream_t)stream;
-  // one pixel per thread: the gathers of a warp then cover contiguous rows (measured 77 us vs 105 us for the
-  // 4-pixels-per-thread mapping at 1080p, cold L2); ZT_WARP_VEC4=1 re-enables the vectorised-store variant
-  static const bool force_vec = getenv("ZT_WARP_VEC4") != nullptr;
+  // 4 pixels per thread with 128-bit stores is the faster mapping on real (smooth) flow: 58 us vs 65 us in the
+  // 1080p frame loop; on a random +-9 px flow the one-pixel mapping wins (77 us vs 105 us, tools/warp_bench.py,
+  // L1-sector bound: profiles/r01_ncu_warp.txt).  ZT_WARP_SCALAR=1 selects the one-pixel mapping.
+  static const bool force_scalar = getenv("ZT_WARP_SCALAR") != nullptr;
   static const int cap = getenv("ZT_WARP_CAP") ? atoi(getenv("ZT_WARP_CAP")) : 64;
-  const bool vec = force_vec && (W & 3) == 0 && ((uintptr_t)out_a & 15) == 0 && (!out_b || ((uintptr_t)out_b & 15) == 0);
+  const bool vec = !force_scalar && (W & 3) == 0 && ((uintptr_t)out_a & 15) == 0 && (!out_b || ((uintptr_t)out_b & 15) == 0);
   if (vec) {
     const int64_t total = (int64_t)H * (W / 4);
     const int blocks = (int)std::min<int64_t>(ceil_div64(total, 256), 16 * kNumSMs);
