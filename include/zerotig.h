@@ -48,6 +48,8 @@ const char* zt_last_error(void);
 int zt_version(void);
 /* number of kernel launches issued through this library since load (bench's gpu_launches) */
 int64_t zt_launch_count(void);
+/* add the kernel count of a replayed CUDA graph (captured launches are counted once, at capture time) */
+int zt_add_launches(int64_t n);
 
 /* ---- generic implicit-GEMM convolution, fp32 CUDA-core path --------------------------------
  * Replaces every nn.Conv2d on the RAFT side (model/RAFT/extractor.py:9-10,44,131,140;

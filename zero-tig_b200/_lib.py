@@ -97,6 +97,7 @@ SIGNATURES = {
     "zt_last_error": [],
     "zt_version": [],
     "zt_launch_count": [],
+    "zt_add_launches": [L],
 }
 _RESTYPE = {"zt_last_error": C.c_char_p, "zt_launch_count": C.c_int64}
 

@@ -54,6 +54,8 @@ struct TcGeom {
   int resident;      // 1: all weights of this N tile stay in shared memory for every pixel tile
   int tmem_cols;     // power of two >= 32, holds two accumulators of BN columns
   int S;             // pixel tiles over all images = tiles_x*tiles_y*B
+  int pdl;           // launched with programmatic stream serialization: prologue + constant weights run early
+  int w_early;       // weights are constants (not produced by the preceding kernel): fetch them before the wait
   long long* trace;  // debug: per-role timestamps of CTA (0,0) (zt_debug_set_tc_trace), else NULL
   int trace_cap;
 };
@@ -169,6 +171,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
   extern __shared__ __align__(1024) uint8_t smem[];
   constexpr int NPART = SPLIT == 3 ? 2 : 1;
   if ((smem_u32(smem) & 1023u) != 0) __trap();     // swizzle atoms need 1024 B alignment
+  // Programmatic dependent launch: let the next kernel of the stream start its prologue (barrier init, TMEM
+  // allocation, constant weights) while this one runs; every warp that touches activations first executes
+  // griddepcontrol.wait (= the preceding grid has completed and flushed).
+  if (g.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TC_BAR_BYTES - 16);
   const uint32_t a_part = (uint32_t)g.a_part, a_stage = a_part * NPART;
   const uint32_t b_part = (uint32_t)g.BN * 128u, b_stage = b_part * NPART;
@@ -208,6 +214,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp < 8) {
+    if (g.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
     // ===================== epilogue: TMEM -> registers -> smem transpose -> global ===========
     // tcgen05.ld hands thread i row i of the tile; a direct store would touch 32 lines per
     // instruction.  Each warp transposes its 32 rows x 32 columns through a padded staging
@@ -436,6 +443,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
   } else if (warp == TC_W_LOAD) {
     // ===================== weight loader (one thread, bulk async copies) =====================
     if (lane == 0) {
+      if (g.pdl && !g.w_early) asm volatile("griddepcontrol.wait;" ::: "memory");
       const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(d.weight) + (size_t)blockIdx.y * nstage * (2u * b_part);
       if (g.resident) {
         if ((int)blockIdx.x < S) {
@@ -521,6 +529,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
     int py = py0, px = px0;
     uint32_t ia = pg;
     TcTracer trace(g, TC_W_PROD + pg);
+    if (g.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
     if (ia < nia) { setup(ia); load_batch(v, pl, py, px); }
     for (; ia < nia; ia += 2) {
       const uint32_t sa = ia % (uint32_t)NA, pa = ((ia / (uint32_t)NA) & 1) ^ 1;
@@ -609,6 +618,10 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
   const ZtConv& d = *dp;
   const int cin = d.c0 + d.c1;
   ZT_REQUIRE(d.in0 && d.weight && d.out, "conv_tc: null pointer");
+  // bit 8 of `split`: the weight operand was produced by the preceding kernel of the stream (all-pairs
+  // correlation: weights = fmap2 packed per frame), so it must not be fetched before that kernel completes
+  const bool w_dynamic = (split & 0x100) != 0;
+  split &= 0xff;
   ZT_REQUIRE(split == 1 || split == 3, "conv_tc: split must be 1 (bf16) or 3 (bf16 hi/lo, 3 products); got %d", split);
   ZT_REQUIRE(BN >= 16 && BN <= 256 && (BN & 15) == 0, "conv_tc: BN=%d must be a multiple of 16 in [16,256]", BN);
   ZT_REQUIRE(d.sh == 1 && d.sw == 1, "conv_tc: stride-1 convolutions only (got %dx%d)", d.sh, d.sw);
@@ -639,6 +652,9 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
   g.S = g.tiles_x * g.tiles_y * d.B;
   g.trace = g_tc_trace;
   g.trace_cap = g_tc_trace_cap;
+  static const bool pdl_on = getenv("ZT_NO_PDL") == nullptr;
+  g.pdl = pdl_on ? 1 : 0;
+  g.w_early = w_dynamic ? 0 : 1;
   g.tmem_cols = 32;
   ZT_REQUIRE(split == 1 || BN <= 128, "conv_tc: the hi/lo split keeps 2*BN accumulator columns, BN=%d > 128", BN);
   while (g.tmem_cols < (split == 3 ? 4 : 2) * BN) g.tmem_cols <<= 1;
@@ -681,7 +697,17 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
                                    227 * 1024));                                                          \
       attr_done = true;                                                                                   \
     }                                                                                                     \
-    conv_tc_kernel<SP, EP, AC><<<grid, TC_THREADS, smem, st>>>(d, g);                                     \
+    if (g.pdl) {                                                                                          \
+      cudaLaunchConfig_t cfg = {};                                                                        \
+      cfg.gridDim = grid; cfg.blockDim = dim3(TC_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;  \
+      cudaLaunchAttribute at[1];                                                                          \
+      at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                                      \
+      at[0].val.programmaticStreamSerializationAllowed = 1;                                               \
+      cfg.attrs = at; cfg.numAttrs = 1;                                                                   \
+      ZT_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_kernel<SP, EP, AC>, d, g));                                \
+    } else {                                                                                              \
+      conv_tc_kernel<SP, EP, AC><<<grid, TC_THREADS, smem, st>>>(d, g);                                   \
+    }                                                                                                     \
   } while (0)
 #define ZT_TC_CASE(EP, AC)                                  \
   if (d.epi == (EP) && ((AC) < 0 || d.act == (AC))) {       \

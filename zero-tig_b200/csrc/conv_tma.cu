@@ -61,6 +61,9 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
                                                                  const TmArgs a, const TmGeom g) {
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
+  // programmatic dependent launch: barrier init, TMEM allocation and the (constant) weight fetch run while the
+  // preceding kernel drains; activations are touched only after griddepcontrol.wait
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TM_BAR_BYTES - 16);
   uint8_t* smA = smem + TM_BAR_BYTES;
   uint8_t* smW = smA + (size_t)g.NA * g.a_stage;
@@ -93,6 +96,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
   if (warp < 8) {
     // ===================== epilogue =====================
     // thread = one pixel (TMEM lane) x 32 consecutive output channels of its half
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int quad = warp & 3, half = warp >> 2;
     const int c0 = half * 32;
     const bool has_cols = c0 < g.BN;
@@ -220,6 +224,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
         for (uint32_t it = 0; it < ntaps; ++it)
           bulk_g2s(smem_u32(smW + it * g.w_tap), a.weight + (size_t)it * g.w_tap, g.w_tap, fullW);
       }
+      asm volatile("griddepcontrol.wait;" ::: "memory");
       uint32_t sa = 0, pa = 1;
       for (int t = blockIdx.x; t < S; t += gridDim.x) {
         const int tyi = t / g.tiles_x, txi = t - tyi * g.tiles_x;
@@ -381,7 +386,7 @@ extern "C" int zt_conv2d_bf16_tma(const ZtConvBf16* dp, void* stream) {
                                    227 * 1024));                                                            \
       attr_done = true;                                                                                     \
     }                                                                                                       \
-    conv_tma_kernel<OUT, ACT><<<gx, TM_THREADS, smem, st>>>(tmap, a, g);                                    \
+    ZT_CUDA(launch_pdl(conv_tma_kernel<OUT, ACT>, dim3(gx), dim3(TM_THREADS), smem, st, tmap, a, g));       \
     return check_launch("conv_tma_kernel");                                                                 \
   } while (0)
   if (d.out_f32) {

@@ -50,6 +50,7 @@ __global__ void __launch_bounds__(128) corr_lookup_kernel(const LookupArgs a, co
                                                           float* __restrict__ out, int out_cs) {
   __shared__ float win[4][10][12];
   __shared__ float frac[4][2];
+  pdl_enter();
   const int n = blockIdx.x;
   const float cx = coords[2 * n], cy = coords[2 * n + 1];
   for (int i = threadIdx.x; i < 400; i += 128) {
@@ -119,6 +120,7 @@ __global__ void __launch_bounds__(64) convex_upsample_kernel(const float* __rest
 __global__ void flow_update_kernel(float* __restrict__ coords1, const float* __restrict__ delta, int d_cs,
                                    float* __restrict__ f1, int f1_cs, float* __restrict__ f2, int f2_cs,
                                    int N, int w8) {
+  pdl_enter();
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   const int y = n / w8, x = n - y * w8;
@@ -163,7 +165,7 @@ extern "C" int zt_corr_lookup_f32(const float* l0, const float* l1, const float*
     // the reference divides by (W-1), (H-1): a 1-pixel level is NaN there; refuse.
     ZT_REQUIRE(hs[i] >= 2 && ws_[i] >= 2, "corr_lookup: pyramid level %d is %dx%d; the reference yields NaN below 2x2", i, hs[i], ws_[i]);
   }
-  corr_lookup_kernel<<<N, 128, 0, (cudaStream_t)stream>>>(a, coords, out, out_cs);
+  ZT_CUDA(launch_pdl(corr_lookup_kernel, dim3(N), dim3(128), 0, (cudaStream_t)stream, a, coords, out, out_cs));
   return check_launch("corr_lookup_kernel");
 }
 
@@ -180,7 +182,7 @@ extern "C" int zt_flow_update_f32(float* coords1, const float* delta, int d_cs, 
   using namespace zt;
   ZT_REQUIRE(coords1 && h8 > 0 && w8 > 0, "flow_update: bad args");
   const int N = h8 * w8;
-  flow_update_kernel<<<ceil_div(N, 128), 128, 0, (cudaStream_t)stream>>>(coords1, delta, d_cs, flow_out, f_cs,
-                                                                        flow_out2, f2_cs, N, w8);
+  ZT_CUDA(launch_pdl(flow_update_kernel, dim3(ceil_div(N, 128)), dim3(128), 0, (cudaStream_t)stream, coords1, delta, d_cs,
+                     flow_out, f_cs, flow_out2, f2_cs, N, w8));
   return check_launch("flow_update_kernel");
 }

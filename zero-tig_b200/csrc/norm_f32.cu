@@ -11,6 +11,7 @@ namespace zt {
 __global__ void __launch_bounds__(256) instnorm_stats_kernel(const float* __restrict__ x, int x_cs,
                                                              double* __restrict__ stats, int HW, int C,
                                                              int pix_per_block) {
+  pdl_enter();
   const int c4n = C >> 2;                 // float4 groups per pixel
   const int lanes = 256 / c4n;            // pixels processed concurrently
   const int cg = threadIdx.x % c4n;
@@ -54,6 +55,7 @@ __global__ void __launch_bounds__(256) instnorm_apply_kernel(const float* __rest
                                                              const double* __restrict__ stats, int HW, int C,
                                                              float eps, int relu_inner, int relu_outer,
                                                              int64_t total4) {
+  pdl_enter();
   const int c4n = C >> 2;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
        i += (int64_t)gridDim.x * blockDim.x) {
@@ -146,8 +148,8 @@ extern "C" int zt_instnorm_nhwc_f32(const float* x, int x_cs, float* out, int ou
   if (int e = check_launch("instnorm_stats_kernel")) return e;
   const int64_t total4 = (int64_t)B * HW * (C >> 2);
   const int blocks = (int)std::min<int64_t>(ceil_div64(total4, 256), 8 * kNumSMs);
-  instnorm_apply_kernel<<<blocks, 256, 0, st>>>(x, x_cs, out, out_cs, res, res_cs, stats, HW, C, eps,
-                                                relu_inner, relu_outer, total4);
+  ZT_CUDA(launch_pdl(instnorm_apply_kernel, dim3(blocks), dim3(256), 0, st, x, x_cs, out, out_cs, res, res_cs, stats, HW, C,
+                     eps, relu_inner, relu_outer, total4));
   return check_launch("instnorm_apply_kernel");
 }
 

@@ -13,6 +13,7 @@ namespace zt {
 // out[b][y][x][(by*2+bx)*C + c] = in[b][2y+by][2x+bx][c]
 __global__ void space_to_depth2_kernel(const float* __restrict__ in, int in_cs, int C, int B, int H, int W,
                                        float* __restrict__ out) {
+  pdl_enter();
   const int c4n = C >> 2, ho = H >> 1, wo = W >> 1;
   const int64_t total = (int64_t)B * ho * wo * 4 * c4n;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -33,6 +34,7 @@ __global__ void space_to_depth2_kernel(const float* __restrict__ in, int in_cs, 
 __global__ void __launch_bounds__(256) convf1_kernel(const float* __restrict__ flow, int f_cs, const float* __restrict__ w,
                                                      const float* __restrict__ bias, float* __restrict__ out, int out_cs,
                                                      int H, int W) {
+  pdl_enter();
   const int lane = threadIdx.x & 31;
   const int pos = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (pos >= H * W) return;
@@ -64,6 +66,7 @@ __global__ void __launch_bounds__(256) convf1_kernel(const float* __restrict__ f
 __global__ void __launch_bounds__(256) conv3x3_n2_kernel(const float* __restrict__ in, int in_cs, int C,
                                                          const float* __restrict__ w, const float* __restrict__ bias,
                                                          float* __restrict__ out, int out_cs, int H, int W) {
+  pdl_enter();
   const int lane = threadIdx.x & 31;
   const int pos = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (pos >= H * W) return;
@@ -104,7 +107,7 @@ extern "C" int zt_space_to_depth2_f32(const float* in, int in_cs, int C, int B, 
   ZT_REQUIRE(H >= 2 && W >= 2 && (H & 1) == 0 && (W & 1) == 0, "space_to_depth2: H, W must be even (got %dx%d)", H, W);
   const int64_t total = (int64_t)B * (H / 2) * (W / 2) * C;
   const int blocks = (int)std::min<int64_t>(ceil_div64(total, 256), 16 * kNumSMs);
-  space_to_depth2_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(in, in_cs, C, B, H, W, out);
+  ZT_CUDA(launch_pdl(space_to_depth2_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, in, in_cs, C, B, H, W, out));
   return check_launch("space_to_depth2_kernel");
 }
 /* flow: [H*W][f_cs] (2 channels used); weight: fp32 [7][7][2][128]; out: [H*W][out_cs] (128 channels, ReLU) */
@@ -113,7 +116,8 @@ extern "C" int zt_raft_convf1_f32(const float* flow, int f_cs, const float* weig
   using namespace zt;
   ZT_REQUIRE(flow && weight && bias && out && f_cs >= 2 && (f_cs & 1) == 0 && out_cs >= 128 && (out_cs & 3) == 0 &&
              H > 0 && W > 0, "raft_convf1: bad args");
-  convf1_kernel<<<ceil_div(H * W, 8), 256, 0, (cudaStream_t)stream>>>(flow, f_cs, weight, bias, out, out_cs, H, W);
+  ZT_CUDA(launch_pdl(convf1_kernel, dim3(ceil_div(H * W, 8)), dim3(256), 0, (cudaStream_t)stream, flow, f_cs, weight, bias,
+                     out, out_cs, H, W));
   return check_launch("convf1_kernel");
 }
 /* in: [H*W][in_cs] with C channels (C % 4 == 0); weight: fp32 [9][C][2]; out[pos][0..1] (stride out_cs), no activation */
@@ -122,6 +126,7 @@ extern "C" int zt_conv3x3_n2_f32(const float* in, int in_cs, int C, const float*
   using namespace zt;
   ZT_REQUIRE(in && weight && bias && out && C > 0 && (C & 3) == 0 && (in_cs & 3) == 0 && in_cs >= C && out_cs >= 2 &&
              H > 0 && W > 0, "conv3x3_n2: bad args");
-  conv3x3_n2_kernel<<<ceil_div(H * W, 8), 256, 0, (cudaStream_t)stream>>>(in, in_cs, C, weight, bias, out, out_cs, H, W);
+  ZT_CUDA(launch_pdl(conv3x3_n2_kernel, dim3(ceil_div(H * W, 8)), dim3(256), 0, (cudaStream_t)stream, in, in_cs, C, weight,
+                     bias, out, out_cs, H, W));
   return check_launch("conv3x3_n2_kernel");
 }

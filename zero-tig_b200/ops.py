@@ -75,6 +75,9 @@ class ConvW:
             src = torch.arange(8, device=w.device)[None, :] ^ (n[:, None] & 7)   # position j <- chunk j^(n&7)
             idx = src.view(1, 1, 1, 1, BN, 8, 1).expand_as(x)
             t = torch.gather(x, 5, idx).contiguous()
+            # constant weights are fetched BEFORE griddepcontrol.wait by the kernel (programmatic dependent
+            # launch): make sure the one-time packing has really finished before the first launch
+            torch.cuda.current_stream().synchronize()
             self._tc[BN] = t
         return t
 
@@ -94,6 +97,7 @@ class ConvW:
             n = torch.arange(BN, device=w.device)
             src = torch.arange(8, device=w.device)[None, :] ^ (n[:, None] & 7)
             t = torch.gather(x, 2, src.view(1, BN, 8, 1).expand_as(x)).contiguous()
+            torch.cuda.current_stream().synchronize()   # fetched before griddepcontrol.wait (see tc_pack)
             self._tc["tma"] = t
         return t
 
@@ -144,7 +148,9 @@ def conv2d(wt: ConvW, in0, in0_cs, c0, B, H, W, out, out_cs, *, in0_off=0, in1=N
         # tensor-core path: tc = 1 (bf16) or 3 (bf16 hi/lo split, 3 products ~ fp32-grade)
         BN = bn or min((wt.cout + 15) // 16 * 16, 128)
         d.weight = _p(wt.tc_pack(BN))
-        check(lib().zt_conv2d_tc_nhwc(C.byref(d), BN, tc, _stream()), "conv2d_tc")
+        # bit 8: weights written by the preceding kernel (RowsAsWeights) - see the PDL note in csrc/conv_tc.cu
+        check(lib().zt_conv2d_tc_nhwc(C.byref(d), BN, tc | (0x100 if isinstance(wt, RowsAsWeights) else 0), _stream()),
+              "conv2d_tc")
     else:
         check(lib().zt_conv2d_nhwc_f32(C.byref(d), _stream()), "conv2d")
     return Ho, Wo
