@@ -187,6 +187,8 @@ class RaftEngine:
 
     # ---- CUDA-graph replay of the whole RAFT pass ----
     USE_GRAPH = _tc_mode("RAFT_GRAPH", 1)
+    PARALLEL = _tc_mode("RAFT_PARALLEL", 1)    # two-stream schedule inside the RAFT pass
+    _side = None
 
     def forward_packed_static(self, x2, hp, wp, iters=12):
         """forward_packed for a STATIC input buffer (update_cache's workspace): the ~200 launches of one RAFT pass
@@ -224,6 +226,40 @@ class RaftEngine:
         assert hp % 8 == 0 and wp % 8 == 0
         h8, w8 = hp // 8, wp // 8
         N = h8 * w8
+        # two-stream schedule (also captured as parallel graph branches): the context network + the per-frame GRU
+        # planes run beside the feature network / correlation pyramid, and inside an iteration convf1/convf2 run
+        # beside lookup/convc1/convc2.  Most RAFT launches fill 30..120 of the 148 SMs, so branches overlap.
+        cur = torch.cuda.current_stream(x2.device)
+        par = bool(self.PARALLEL)
+        if par and (self._side is None or self._side.device != x2.device):
+            self._side = torch.cuda.Stream(x2.device)
+        side = self._side if par else cur
+
+        def fork():
+            if par:
+                ev = torch.cuda.Event()
+                ev.record(cur)
+                side.wait_event(ev)
+
+        def join():
+            if par:
+                ev = torch.cuda.Event()
+                ev.record(side)
+                cur.wait_event(ev)
+        hx = ws.get("hx", (N, 384))
+        gru_pre = {}
+        fork()
+        with torch.cuda.stream(side):
+            c, ch, cwid = self._encoder("cnet", x2, 1, hp, wp, True)
+            ops.conv2d(w["cnet.conv2.net"], c, 128, 128, 1, h8, w8, hx, 384, act="tanh", tc=T, bn=64)
+            ops.conv2d(w["cnet.conv2.inp"], c, 128, 128, 1, h8, w8, hx, 384, out_off=128, act="relu", tc=T, bn=64)
+            if self.TC_UPD:
+                for s_, pad_ in (("1", (0, 2)), ("2", (2, 0))):
+                    for kind, co in (("zr", 256), ("q", 128)):
+                        P = ws.get(f"gru.pre.{kind}{s_}", (N, co))
+                        ops.conv2d(w[f"gru.{kind}{s_}.inp"], hx, 384, 128, 1, h8, w8, P, co, in0_off=128, pad=pad_,
+                                   tc=self.TC_UPD, bn=64)
+                        gru_pre[kind + s_] = P
         # feature network on both images
         f, fh, fw = self._encoder("fnet", x2, 2, hp, wp, False)
         assert (fh, fw) == (h8, w8)
@@ -256,11 +292,6 @@ class RaftEngine:
             ops.conv2d(cw, fmap, 256, 256, 1, h8, w8, lv[0], N, scale=0.0625)
         for i in range(3):
             ops.avgpool2(lv[i], lv[i + 1], N, hs[i], wsz[i])
-        # context network
-        c, ch, cwid = self._encoder("cnet", x2, 1, hp, wp, True)
-        hx = ws.get("hx", (N, 384))
-        ops.conv2d(w["cnet.conv2.net"], c, 128, 128, 1, h8, w8, hx, 384, act="tanh", tc=T, bn=64)
-        ops.conv2d(w["cnet.conv2.inp"], c, 128, 128, 1, h8, w8, hx, 384, out_off=128, act="relu", tc=T, bn=64)
         # iteration state
         grid = ws.bufs.get(("grid", h8, w8))
         if grid is None:
@@ -281,22 +312,20 @@ class RaftEngine:
         delta = ws.get("delta", (N, 4), zero=True)
         ops.flow_update(coords1, None, 0, flow4, 4, hx, 384, 382, h8, w8)
         T = self.TC_UPD
-        gru_pre = {}
-        if T:
-            for s, pad in (("1", (0, 2)), ("2", (2, 0))):
-                for kind, co in (("zr", 256), ("q", 128)):
-                    P = ws.get(f"gru.pre.{kind}{s}", (N, co))
-                    ops.conv2d(w[f"gru.{kind}{s}.inp"], hx, 384, 128, 1, h8, w8, P, co, in0_off=128, pad=pad, tc=T, bn=64)
-                    gru_pre[kind + s] = P
+        join()   # context network, hidden state and GRU planes are ready
         for it in range(iters):
-            ops.corr_lookup(lv, hs, wsz, coords1, corr, 324, N)
+            fork()
+            with torch.cuda.stream(side):     # flow branch of the motion encoder (update.py:92-93)
+                if T:
+                    ops.raft_convf1(flow4, 4, w["enc.convf1.raw"][0], w["enc.convf1.raw"][1], f1, 128, h8, w8)
+                else:
+                    ops.conv2d(w["enc.convf1"], flow4, 4, 4, 1, h8, w8, f1, 128, pad=(3, 3), act="relu", tc=T, bn=64)
+                ops.conv2d(w["enc.convf2"], f1, 128, 128, 1, h8, w8, c2f, 256, out_off=192, pad=(1, 1), act="relu", tc=T,
+                           bn=32)
+            ops.corr_lookup(lv, hs, wsz, coords1, corr, 324, N)   # correlation branch (update.py:90-91)
             ops.conv2d(w["enc.convc1"], corr, 324, 324, 1, h8, w8, c1, 256, act="relu", tc=T, bn=64)
             ops.conv2d(w["enc.convc2"], c1, 256, 256, 1, h8, w8, c2f, 256, pad=(1, 1), act="relu", tc=T, bn=64)
-            if T:
-                ops.raft_convf1(flow4, 4, w["enc.convf1.raw"][0], w["enc.convf1.raw"][1], f1, 128, h8, w8)
-            else:
-                ops.conv2d(w["enc.convf1"], flow4, 4, 4, 1, h8, w8, f1, 128, pad=(3, 3), act="relu", tc=T, bn=64)
-            ops.conv2d(w["enc.convf2"], f1, 128, 128, 1, h8, w8, c2f, 256, out_off=192, pad=(1, 1), act="relu", tc=T, bn=32)
+            join()
             ops.conv2d(w["enc.conv"], c2f, 256, 256, 1, h8, w8, hx, 384, out_off=256, pad=(1, 1), act="relu", tc=T, bn=64)
             for s, pad in (("1", (0, 2)), ("2", (2, 0))):
                 if T:
