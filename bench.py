@@ -275,7 +275,7 @@ def run_b200(args):
         # ---- per-kernel pass (rank 0): shares + roofline of the dominant kernels ----
         eng = model.raft.engine()
         use_graph, eng.USE_GRAPH = eng.USE_GRAPH, 0     # per-call events need the eager (un-graphed) RAFT pass
-        with OpTimer(ops, ["conv2d", "conv2d_bf16", "warp_pair", "corr_lookup", "avgpool2", "instnorm"]) as ot:
+        with OpTimer(ops, ["conv2d", "conv2d_bf16", "warp_pair", "corr_lookup", "corr_pyramid", "avgpool2", "instnorm"]) as ot:
             nprof = min(K, 5)
             for i in range(nprof):
                 step_dev(i)
@@ -285,7 +285,8 @@ def run_b200(args):
         raft_ms = tot["conv_raft"][0] / nprof
         warp_ms = tot["warp_pair"][0] / nprof
         look_ms = tot["corr_lookup"][0] / tot["corr_lookup"][1]
-        corr_ms = (tot["corr_volume"][0] + tot["avgpool2"][0]) / nprof
+        # fused path: zt_corr_pyramid_f32 (pack + one tcgen05 kernel); ZT_CORR_FUSED=0: 1x1 GEMM + 3 avg-pool kernels
+        corr_ms = sum(tot[k][0] for k in ("corr_pyramid", "corr_volume", "avgpool2") if k in tot) / nprof
         # the tcgen05 convolutions of the three full-resolution Retinex nets (conv_tma_kernel: bf16 NHWC
         # activations moved by TMA).  Algorithmic bytes = every input/output/residual activation once;
         # algorithmic flops = 2*M*cout*cin*taps of the reference layers (no padding counted).

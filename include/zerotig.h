@@ -104,6 +104,14 @@ int zt_instnorm_nhwc_f32(const float* x, int x_cs, float* out, int out_cs,
 int zt_transpose_f32(const float* in, int R, int C, int in_rs, float* out, int out_rs, void* stream);
 /* F.avg_pool2d(x,2,stride=2) over `planes` planes of h x w -> (h/2) x (w/2)  (corr.py:26) */
 int zt_avgpool2_f32(const float* in, float* out, int64_t planes, int h, int w, void* stream);
+/* CorrBlock.__init__ (corr.py:13-27) + CorrBlock.corr (corr.py:52-60) in one pass: fmap [2*h0*w0][fm_rs]
+ * (rows 0..N-1 = fmap1, N..2N-1 = fmap2, 256 channels) -> level l [N][hl][wl], hl = h0 >> l (floor),
+ * level 0 = <fmap1[n], fmap2[m]> / 16, levels 1..3 = successive 2x2 means.  tcgen05 GEMM (bf16 hi/lo
+ * split, fp32 accumulate) fed by TMA; all four levels are written from the same accumulator.
+ * scratch: zt_corr_pyramid_scratch_bytes(h0, w0) bytes, 128-byte aligned. */
+int64_t zt_corr_pyramid_scratch_bytes(int h0, int w0);
+int zt_corr_pyramid_f32(const float* fmap, int fm_rs, int h0, int w0, float* l0, float* l1, float* l2,
+                        float* l3, void* scratch, int64_t scratch_bytes, void* stream);
 /* CorrBlock.__call__ (corr.py:29-50) + bilinear_sampler (utils/utils.py:285-299):
  * coords [N][2] (x,y), pyramid level l is [N][hl][wl]; out [N][out_cs], channel
  * l*81 + a*9 + b samples level l at (x/2^l + a-4, y/2^l + b-4)  (x-offset major). */

@@ -165,6 +165,58 @@ def test_corr_volume_pyramid_vs_reference_golden(gold, dev):
         np.testing.assert_allclose(lv[i].cpu().numpy(), ref, rtol=0, atol=2e-5)
 
 
+def _fused_pyramid(fm1, fm2, dev):
+    """zt_corr_pyramid_f32: volume + three pooled levels from one tcgen05 accumulator."""
+    from zero_tig_b200 import ops
+    _, D, h, w = fm1.shape
+    N = h * w
+    fmap = torch.cat([nhwc(fm1), nhwc(fm2)], 0).contiguous()
+    hs, ws = [h], [w]
+    for _ in range(3):
+        hs.append(hs[-1] // 2)
+        ws.append(ws[-1] // 2)
+    lv = [torch.full((N, max(hs[i] * ws[i], 1)), float("nan"), device=dev) for i in range(4)]
+    scratch = torch.empty(ops.corr_pyramid_scratch_bytes(h, w) // 4, device=dev)
+    ops.corr_pyramid(fmap, D, h, w, lv, scratch)
+    return lv, hs, ws
+
+
+def test_corr_pyramid_fused_vs_reference_golden(gold, dev):
+    lv, hs, ws = _fused_pyramid(torch.from_numpy(gold["corr_f1"]), torch.from_numpy(gold["corr_f2"]), dev)
+    for i in range(4):
+        ref = gold[f"corr_pyr{i}"].reshape(90, -1)
+        if ref.shape[1]:
+            # bf16 hi/lo split (3 of 4 partial products), fp32 accumulation: 2e-5 abs on |corr| ~ 1
+            np.testing.assert_allclose(lv[i].cpu().numpy(), ref, rtol=0, atol=2e-5)
+
+
+@pytest.mark.parametrize("h,w", [(8, 8), (16, 16), (17, 23), (13, 9), (45, 80), (34, 61)])
+def test_corr_pyramid_fused_vs_oracle(dev, h, w):
+    import zt_oracle as O
+    g = torch.Generator().manual_seed(h * 100 + w)
+    f1 = torch.randn(1, 256, h, w, generator=g)
+    f2 = torch.randn(1, 256, h, w, generator=g)
+    pyr = O.corr_pyramid(f1, f2)
+    lv, hs, ws = _fused_pyramid(f1, f2, dev)
+    for i in range(4):
+        ref = pyr[i].reshape(h * w, -1)
+        if ref.shape[1]:
+            got = lv[i].cpu()
+            assert torch.isfinite(got).all(), f"level {i}: unwritten entries"
+            # bf16 hi/lo split drops the lo*lo partial product (2^-16 relative per term); |corr| reaches ~5 here
+            assert (got - ref).abs().max().item() < 5e-5, (i, (got - ref).abs().max().item())
+
+
+def test_corr_pyramid_fused_rejects_bad_args(dev):
+    from zero_tig_b200 import ops
+    t = torch.zeros(64, device=dev)
+    with pytest.raises(RuntimeError):
+        ops.corr_pyramid(t, 256, 4, 4, [t, t, t, t], t)          # grid below 8x8
+    f = torch.zeros(2 * 64, 256, device=dev)
+    with pytest.raises(RuntimeError):
+        ops.corr_pyramid(f, 256, 8, 8, [t, t, t, t], t)          # scratch too small
+
+
 def test_corr_lookup_vs_reference_golden(gold, dev):
     from zero_tig_b200 import ops
     pyr = [torch.from_numpy(gold[f"lookup_pyr{i}"]) for i in range(4)]

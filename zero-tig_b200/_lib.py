@@ -56,6 +56,8 @@ SIGNATURES = {
     "zt_transpose_f32": [P, I, I, I, P, I, P],
     "zt_avgpool2_f32": [P, P, L, I, I, P],
     "zt_corr_lookup_f32": [P, P, P, P, IP, IP, P, P, I, I, P],
+    "zt_corr_pyramid_scratch_bytes": [I, I],
+    "zt_corr_pyramid_f32": [P, I, I, I, P, P, P, P, P, L, P],
     "zt_convex_upsample_f32": [P, I, P, I, P, I, I, P],
     "zt_flow_update_f32": [P, P, I, P, I, P, I, I, I, P],
     "zt_resize255_f32": [P, I, I, I, I, I, P, I, I, P, P, P],
@@ -99,7 +101,7 @@ SIGNATURES = {
     "zt_launch_count": [],
     "zt_add_launches": [L],
 }
-_RESTYPE = {"zt_last_error": C.c_char_p, "zt_launch_count": C.c_int64}
+_RESTYPE = {"zt_last_error": C.c_char_p, "zt_launch_count": C.c_int64, "zt_corr_pyramid_scratch_bytes": C.c_int64}
 
 _lib = None
 

@@ -4,6 +4,8 @@ The engines read parameters from the (reference-compatible) nn.Module containers
 re-layout them once per device / parameter version, own the NHWC workspaces and issue
 the kernel sequence on torch's current stream.  Nothing here computes on the CPU.
 """
+import os
+
 import torch
 
 from . import ops
@@ -53,6 +55,7 @@ class RaftEngine:
     TC_UPD = _tc_mode("RAFT_UPD", TC)      # motion encoder + GRU
     TC_HEAD = _tc_mode("RAFT_HEAD", TC)    # flow head + mask head
     TC_CORR = _tc_mode("RAFT_CORR", 3 if TC else 0)   # all-pairs correlation volume
+    CORR_FUSED = int(os.environ.get("ZT_CORR_FUSED", "1"))   # volume + pyramid in one kernel (corr_gemm.cu)
 
     def __init__(self, raft):
         self.raft = raft
@@ -274,7 +277,11 @@ class RaftEngine:
             raise RuntimeError("RAFT grid %dx%d is too small: the reference's 4-level lookup yields NaN when the "
                                "coarsest level is below 2x2 (needs a feature grid >= 16x16)" % (h8, w8))
         lv = [ws.get(f"corr{i}", (N, hs[i] * wsz[i])) for i in range(4)]
-        if self.TC_CORR:
+        if self.TC_CORR and self.CORR_FUSED:
+            # volume + all three pooled levels from one tcgen05 accumulator (corr_gemm.cu)
+            scratch = ws.get("corr_scratch", (ops.corr_pyramid_scratch_bytes(h8, w8) // 4,))
+            ops.corr_pyramid(fmap, 256, h8, w8, lv, scratch)
+        elif self.TC_CORR:
             # fmap1 x fmap2^T / sqrt(256) on the tensor cores (hi/lo split): fmap2 is packed as the
             # "weights" of a 1x1 convolution with cout = N
             cw = ws.bufs.get(("corr_w", N))
@@ -290,8 +297,9 @@ class RaftEngine:
             cw = ConvW.__new__(ConvW)
             cw.w, cw.b, cw.kh, cw.kw, cw.cin, cw.cout, cw.w_cs = f2t, None, 1, 1, 256, N, N4
             ops.conv2d(cw, fmap, 256, 256, 1, h8, w8, lv[0], N, scale=0.0625)
-        for i in range(3):
-            ops.avgpool2(lv[i], lv[i + 1], N, hs[i], wsz[i])
+        if not (self.TC_CORR and self.CORR_FUSED):
+            for i in range(3):
+                ops.avgpool2(lv[i], lv[i + 1], N, hs[i], wsz[i])
         # iteration state
         grid = ws.bufs.get(("grid", h8, w8))
         if grid is None:

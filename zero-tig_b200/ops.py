@@ -218,6 +218,17 @@ def avgpool2(x, out, planes, h, w):
     check(lib().zt_avgpool2_f32(_p(x), _p(out), planes, h, w, _stream()), "avgpool2")
 
 
+def corr_pyramid_scratch_bytes(h0, w0):
+    return int(lib().zt_corr_pyramid_scratch_bytes(h0, w0))
+
+
+def corr_pyramid(fmap, fm_rs, h0, w0, levels, scratch):
+    """All-pairs correlation + 4-level pyramid in one tcgen05 kernel (corr.py:13-27,52-60)."""
+    check(lib().zt_corr_pyramid_f32(_p(fmap), fm_rs, h0, w0, _p(levels[0]), _p(levels[1]), _p(levels[2]),
+                                    _p(levels[3]), _p(scratch), scratch.numel() * scratch.element_size(), _stream()),
+          "corr_pyramid")
+
+
 def corr_lookup(levels, hs, ws, coords, out, out_cs, N):
     IA = C.c_int * 4
     check(lib().zt_corr_lookup_f32(_p(levels[0]), _p(levels[1]), _p(levels[2]), _p(levels[3]),
