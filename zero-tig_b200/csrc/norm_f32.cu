@@ -22,7 +22,21 @@ __global__ void __launch_bounds__(256) instnorm_stats_kernel(const float* __rest
   double s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
   if (pl < lanes) {
     const float* base = x + (int64_t)b * HW * x_cs + cg * 4;
-    for (int p = p0 + pl; p < p1; p += lanes) {
+    int p = p0 + pl;
+    // four independent loads in flight per thread; the sums stay in fp64 (no cancellation problem later)
+    for (; p + 3 * lanes < p1; p += 4 * lanes) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = __ldg(reinterpret_cast<const float4*>(base + (int64_t)(p + u * lanes) * x_cs));
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        s[0] += v[u].x; q[0] += (double)v[u].x * v[u].x;
+        s[1] += v[u].y; q[1] += (double)v[u].y * v[u].y;
+        s[2] += v[u].z; q[2] += (double)v[u].z * v[u].z;
+        s[3] += v[u].w; q[3] += (double)v[u].w * v[u].w;
+      }
+    }
+    for (; p < p1; p += lanes) {
       const float4 v = __ldg(reinterpret_cast<const float4*>(base + (int64_t)p * x_cs));
       s[0] += v.x; q[0] += (double)v.x * v.x;
       s[1] += v.y; q[1] += (double)v.y * v.y;
@@ -30,39 +44,43 @@ __global__ void __launch_bounds__(256) instnorm_stats_kernel(const float* __rest
       s[3] += v.w; q[3] += (double)v.w * v.w;
     }
   }
-  __shared__ double red[256][8];
+  // red[pixel lane][channel group][sum x4 | sumsq x4]; one thread per (channel group, entry) folds the pixel lanes
+  __shared__ double red[256 * 8];
 #pragma unroll
-  for (int e = 0; e < 4; ++e) { red[threadIdx.x][e] = s[e]; red[threadIdx.x][4 + e] = q[e]; }
+  for (int e = 0; e < 4; ++e) { red[threadIdx.x * 8 + e] = s[e]; red[threadIdx.x * 8 + 4 + e] = q[e]; }
   __syncthreads();
-  // threads 0..c4n-1 reduce over pixel lanes for their channel group
-  if (threadIdx.x < c4n) {
-    double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int l = 0; l < lanes; ++l)
-#pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] += red[l * c4n + threadIdx.x][e];
-    double* dst = stats + ((int64_t)b * C + threadIdx.x * 4) * 2;
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      atomicAdd(dst + e * 2 + 0, acc[e]);
-      atomicAdd(dst + e * 2 + 1, acc[4 + e]);
-    }
+  for (int j = threadIdx.x; j < c4n * 8; j += 256) {
+    double acc = 0;
+    for (int l = 0; l < lanes; ++l) acc += red[l * c4n * 8 + j];
+    const int g4 = j >> 3, e = j & 7;
+    // stats layout: [b][c][sum, sumsq]
+    atomicAdd(stats + ((int64_t)b * C + g4 * 4 + (e & 3)) * 2 + (e >> 2), acc);
   }
 }
 
+// mean / 1/std of every (image, channel) once per block into shared memory, then a streaming normalise
 __global__ void __launch_bounds__(256) instnorm_apply_kernel(const float* __restrict__ x, int x_cs,
                                                              float* __restrict__ out, int out_cs,
                                                              const float* __restrict__ res, int res_cs,
-                                                             const double* __restrict__ stats, int HW, int C,
+                                                             const double* __restrict__ stats, int HW, int C, int BC,
                                                              float eps, int relu_inner, int relu_outer,
                                                              int64_t total4) {
+  extern __shared__ float2 mr[];          // [b*C + c] = (mean, rstd)
   pdl_enter();
+  for (int i = threadIdx.x; i < BC; i += blockDim.x) {
+    const double mean = stats[2 * i] / HW;
+    double var = stats[2 * i + 1] / HW - mean * mean;   // biased variance
+    var = var < 0 ? 0 : var;
+    mr[i] = make_float2((float)mean, (float)(1.0 / sqrt(var + (double)eps)));
+  }
+  __syncthreads();
   const int c4n = C >> 2;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
        i += (int64_t)gridDim.x * blockDim.x) {
     const int cg = (int)(i % c4n);
     const int64_t pix = i / c4n;          // b*HW + p
     const int b = (int)(pix / HW);
-    const double* st = stats + ((int64_t)b * C + cg * 4) * 2;
+    const float2* st = mr + b * C + cg * 4;
     float4 v = __ldg(reinterpret_cast<const float4*>(x + pix * x_cs + cg * 4));
     float r[4] = {v.x, v.y, v.z, v.w};
     float4 rv = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -70,11 +88,7 @@ __global__ void __launch_bounds__(256) instnorm_apply_kernel(const float* __rest
     const float rr[4] = {rv.x, rv.y, rv.z, rv.w};
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
-      const double mean = st[e * 2] / HW;
-      double var = st[e * 2 + 1] / HW - mean * mean;   // biased variance
-      var = var < 0 ? 0 : var;
-      const float rstd = (float)(1.0 / sqrt(var + (double)eps));
-      float y = (r[e] - (float)mean) * rstd;
+      float y = (r[e] - st[e].x) * st[e].y;
       if (relu_inner) y = fmaxf(y, 0.f);
       if (res) y += rr[e];
       if (relu_outer) y = fmaxf(y, 0.f);
@@ -139,7 +153,7 @@ extern "C" int zt_instnorm_nhwc_f32(const float* x, int x_cs, float* out, int ou
   ZT_REQUIRE(x && out && stats, "instnorm: null pointer");
   ZT_REQUIRE((C & 3) == 0 && C <= 1024 && (x_cs & 3) == 0 && (out_cs & 3) == 0 && (!res || (res_cs & 3) == 0),
              "instnorm: C and strides must be multiples of 4 (C=%d)", C);
-  ZT_REQUIRE(B > 0 && HW > 0, "instnorm: bad dims");
+  ZT_REQUIRE(B > 0 && HW > 0 && (int64_t)B * C <= 6144, "instnorm: bad dims (B*C must be <= 6144)");
   cudaStream_t st = (cudaStream_t)stream;
   ZT_CUDA(cudaMemsetAsync(stats, 0, sizeof(double) * 2 * B * C, st));
   const int slabs = max(1, min(ceil_div(HW, 64), (4 * kNumSMs) / B));
@@ -148,8 +162,8 @@ extern "C" int zt_instnorm_nhwc_f32(const float* x, int x_cs, float* out, int ou
   if (int e = check_launch("instnorm_stats_kernel")) return e;
   const int64_t total4 = (int64_t)B * HW * (C >> 2);
   const int blocks = (int)std::min<int64_t>(ceil_div64(total4, 256), 8 * kNumSMs);
-  ZT_CUDA(launch_pdl(instnorm_apply_kernel, dim3(blocks), dim3(256), 0, st, x, x_cs, out, out_cs, res, res_cs, stats, HW, C,
-                     eps, relu_inner, relu_outer, total4));
+  ZT_CUDA(launch_pdl(instnorm_apply_kernel, dim3(blocks), dim3(256), (size_t)B * C * sizeof(float2), st, x, x_cs, out, out_cs,
+                     res, res_cs, stats, HW, C, B * C, eps, relu_inner, relu_outer, total4));
   return check_launch("instnorm_apply_kernel");
 }
 

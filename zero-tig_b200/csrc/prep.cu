@@ -71,25 +71,45 @@ __global__ void __launch_bounds__(256) resize255_kernel(const float* __restrict_
   }
 }
 
-// torchvision _scale_channel, integer exact.  One thread per channel (256 serial steps).
-__global__ void equalize_lut_kernel(const int* __restrict__ hist, uint8_t* __restrict__ lut) {
-  const int c = threadIdx.x;
-  if (c >= 3) return;
-  const int* h = hist + c * 256;
-  long long total = 0;
+// torchvision _scale_channel, integer exact.  One block per channel, one thread per bin: block-wide total / last
+// non-zero bin, warp-scan prefix sum, one 64-bit division per thread.
+__global__ void __launch_bounds__(256) equalize_lut_kernel(const int* __restrict__ hist, uint8_t* __restrict__ lut) {
+  pdl_enter();
+  const int c = blockIdx.x, i = threadIdx.x, lane = i & 31, w = i >> 5;
+  __shared__ long long wsum[8];
+  __shared__ int wlast[8];
+  const int hi = hist[c * 256 + i];
+  // inclusive prefix sum of the histogram
+  long long incl = hi;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const long long t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  int last = hi != 0 ? i : -1;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) last = max(last, __shfl_xor_sync(0xffffffffu, last, o));
+  if (lane == 31) wsum[w] = incl;
+  if (lane == 0) wlast[w] = last;
+  __syncthreads();
+  long long before = 0, total = 0;
   int last_nz = -1;
-  for (int i = 0; i < 256; ++i) { total += h[i]; if (h[i] != 0) last_nz = i; }
-  const long long step = last_nz >= 0 ? (total - h[last_nz]) / 255 : 0;   // sum(nonzero_hist[:-1]) // 255
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    if (k < w) before += wsum[k];
+    total += wsum[k];
+    last_nz = max(last_nz, wlast[k]);
+  }
+  const long long cum = before + incl;                                    // sum(h[0..i])
+  const long long step = last_nz >= 0 ? (total - hist[c * 256 + last_nz]) / 255 : 0;   // sum(nonzero_hist[:-1]) // 255
   uint8_t* l = lut + c * 256;
   if (step == 0) {
-    for (int i = 0; i < 256; ++i) l[i] = (uint8_t)i;                      // identity
+    l[i] = (uint8_t)i;                                                     // identity
     return;
   }
-  long long cum = 0;
-  l[0] = 0;
-  for (int i = 0; i < 255; ++i) {
-    cum += h[i];
-    long long v = (cum + step / 2) / step;                                 // shifted right by one bin
+  if (i == 0) l[0] = 0;
+  if (i < 255) {
+    const long long v = (cum + step / 2) / step;                           // shifted right by one bin
     l[i + 1] = (uint8_t)(v > 255 ? 255 : v);
   }
 }
@@ -202,7 +222,7 @@ extern "C" int zt_resize255_f32(const float* img, int H, int W, int ht, int wd, 
 extern "C" int zt_equalize_lut(const int* hist, uint8_t* lut, void* stream) {
   using namespace zt;
   ZT_REQUIRE(hist && lut, "equalize_lut: null pointer");
-  equalize_lut_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(hist, lut);
+  equalize_lut_kernel<<<3, 256, 0, (cudaStream_t)stream>>>(hist, lut);
   return check_launch("equalize_lut_kernel");
 }
 
