@@ -17,6 +17,9 @@ CASES = {
     "k1_512": (512, 64, 1, 1, (0, 0), 540, 960, 1, "plain"),
     "k1x3_256": (256, 64, 1, 3, (0, 1), 540, 960, 1, "plain"),
     "enc_l1": (64, 64, 3, 3, (1, 1), 180, 320, 2, "plain"),
+    "gru_zr256": (256, 256, 1, 5, (0, 2), 45, 80, 1, "plain"),
+    "gru_v256": (256, 256, 5, 1, (2, 0), 45, 80, 1, "plain"),
+    "convc2": (256, 192, 3, 3, (1, 1), 45, 80, 1, "plain"),
 }
 
 

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mma(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
   asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
@@ -15,7 +16,7 @@ __device__ __forceinline__ uint64_t desc_none(uint32_t addr, uint32_t lbo, uint3
   return (uint64_t)((addr >> 4) & 0x3FFF) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) | ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) | (1ull << 46);
 }
 // mode bits: 0 = vary A k-slice, 1 = vary B k-slice, 2 = vary A row offset (tap), 3 = no-swizzle layout
-__global__ void bench(int N, int mode, int iters, long long* out) {
+__global__ void bench(int N, int mode, int iters, long long* out, uint32_t tcols, int issuer) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ uint64_t bar;
   __shared__ uint32_t tslot;
@@ -25,14 +26,14 @@ __global__ void bench(int N, int mode, int iters, long long* out) {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tslot)), "r"(256u) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tslot)), "r"(tcols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tm = tslot;
-  if (threadIdx.x == 0) {
+  if (threadIdx.x == issuer) {
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | (8u << 24);
     const uint32_t a0 = smem_u32(smem), b0 = a0 + 64 * 1024;
     const bool nosw = mode & 8;
@@ -60,17 +61,21 @@ __global__ void bench(int N, int mode, int iters, long long* out) {
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
-  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tm), "r"(256u) : "memory");
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tm), "r"(tcols) : "memory");
 }
-int main() {
+int main(int argc, char** argv) {
+  const int threads = argc > 1 ? atoi(argv[1]) : 128;
+  const uint32_t tcols = argc > 2 ? atoi(argv[2]) : 256;
+  const int issuer = argc > 3 ? atoi(argv[3]) : 0;
+  const int smem_kb = argc > 4 ? atoi(argv[4]) : 200;
   long long* d; cudaMalloc(&d, 16);
-  cudaFuncSetAttribute(bench, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  cudaFuncSetAttribute(bench, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_kb * 1024);
   const int iters = 720;
   const int Ns[] = {16, 64, 128, 256};
-  for (int nosw = 0; nosw < 2; ++nosw)
+  for (int nosw = 0; nosw < 1; ++nosw)
     for (int N : Ns)
-      for (int mode = 0; mode < 8; ++mode) {
-        bench<<<1, 128, 200 * 1024>>>(N, mode | (nosw << 3), iters, d);
+      for (int mode = 3; mode < 4; ++mode) {
+        bench<<<1, threads, smem_kb * 1024>>>(N, mode | (nosw << 3), iters, d, tcols, issuer);
         long long h[2];
         cudaError_t e = cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return 1; }

@@ -10,7 +10,7 @@ cs = (cin + 3) // 4 * 4
 x = torch.randn(B * H * W, cs, device="cuda"); w = torch.randn(cout, cin, kh, kw, device="cuda") * 0.05
 wt = ops.ConvW(w, torch.zeros(cout, device="cuda")); ocs = (cout + 3) // 4 * 4
 out = torch.empty(B * H * W, ocs, device="cuda")
-kw_ = dict(pad=pad, act="relu", tc=tc)
+kw_ = dict(pad=pad, act="relu", tc=tc, bn=int(os.environ.get("BN", "64")))
 if epi == "add": kw_.update(epi="add", aux0=x, aux0_cs=cs)
 for _ in range(3): ops.conv2d(wt, x, cs, wt.cin, B, H, W, out, ocs, **kw_)
 cap = 4000
@@ -30,7 +30,7 @@ for role in range(NR):
 ev.sort()
 t0 = ev[0][0]
 names = {8: "MMA", 10: "PG0", 11: "PG1"}
-evn = {"MMA": {0: "waitA", 1: "gotA", 2: "issued", 3: "waitAcc", 4: "gotAcc"}, "P": {0: "waitSlot", 1: "gotSlot", 2: "stored", 3: "arrived"},
+evn = {"MMA": {0: "waitA", 1: "gotA", 2: "issued", 3: "waitAcc", 4: "gotAcc", 5: "tap>", 6: "tap<"}, "P": {0: "waitSlot", 1: "gotSlot", 2: "stored", 3: "arrived"},
        "E": {0: "waitAcc", 1: "gotAcc", 2: "done"}}
 lo = int(sys.argv[4]) if len(sys.argv) > 4 else 0
 hi = int(sys.argv[5]) if len(sys.argv) > 5 else 400

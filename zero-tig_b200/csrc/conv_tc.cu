@@ -33,8 +33,7 @@ constexpr int TC_TW = 8;          // tile width in pixels (= one 8-row core-matr
 constexpr int TC_TH = 16;         // tile height -> 128 GEMM rows
 constexpr int TC_CG = 64;         // channels per A stage: one 128 B swizzled row per pixel
 // warps 0-7 epilogue (warp%4 = TMEM lane quadrant, warp/4 = odd/even 16-column groups),
-// 8 MMA issuer, 9 weight loader, 10-13 producer group 0, 14-17 producer group 1
-// (the producer groups alternate A stages)
+// 8 MMA issuer, 9 weight loader, 10-17 producers (all 256 threads fill each A stage together)
 constexpr int TC_THREADS = 576;
 constexpr int TC_PB = 12;         // patch pixels (float4 loads) in flight per producer thread
 constexpr int TC_W_MMA = 8, TC_W_LOAD = 9, TC_W_PROD = 10;
@@ -56,6 +55,8 @@ struct TcGeom {
   int S;             // pixel tiles over all images = tiles_x*tiles_y*B
   int pdl;           // launched with programmatic stream serialization: prologue + constant weights run early
   int w_early;       // weights are constants (not produced by the preceding kernel): fetch them before the wait
+  int a_off, epi_off;  // byte offsets of the A ring and of the epilogue staging tile (aliased onto the A ring when a CTA
+                     // owns a single pixel tile: the ring is dead once the accumulator is complete)
   long long* trace;  // debug: per-role timestamps of CTA (0,0) (zt_debug_set_tc_trace), else NULL
   int trace_cap;
 };
@@ -178,7 +179,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TC_BAR_BYTES - 16);
   const uint32_t a_part = (uint32_t)g.a_part, a_stage = a_part * NPART;
   const uint32_t b_part = (uint32_t)g.BN * 128u, b_stage = b_part * NPART;
-  uint8_t* smA = smem + TC_BAR_BYTES + TC_EPI_BYTES;   // 1024 B aligned (swizzle atoms)
+  uint8_t* smA = smem + g.a_off;                       // 1024 B aligned (swizzle atoms)
   uint8_t* smB = smA + g.NA * a_stage;
   const uint32_t bar0 = smem_u32(smem);
   const int NA = g.NA, NB = g.NB;
@@ -198,7 +199,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
   const uint32_t nstage = (uint32_t)ngroups * ntaps;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < NA; ++s) { mbar_init(fullA(s), 128); mbar_init(emptyA(s), 1); }
+    for (int s = 0; s < NA; ++s) { mbar_init(fullA(s), 8); mbar_init(emptyA(s), 1); }
     for (int s = 0; s < NBb; ++s) { mbar_init(fullB(s), 1); mbar_init(emptyB(s), 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(accFull(s), 1); mbar_init(accEmpty(s), 256); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -221,7 +222,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
     // tile so that 8 lanes cover 128 contiguous bytes of one pixel (4 full lines per
     // instruction) for the residual/gate loads and the output stores alike.
     const int quad = warp & 3, half = warp >> 2;
-    float* stage = reinterpret_cast<float*>(smem + TC_BAR_BYTES) + warp * 32 * TC_EPI_LD;
+    float* stage = reinterpret_cast<float*>(smem + g.epi_off) + warp * 32 * TC_EPI_LD;
     const int piece = lane & 7, rsub = lane >> 3;
     const int nend = min(d.cout, n0 + g.BN);        // this CTA owns output channels [n0, nend)
     const int nchunk = (nend - n0 + 31) >> 5;
@@ -384,55 +385,67 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
           tc_fence_after();
           if (lane == 0) trace(lt * ngroups + gi, 1);
           const int nks = crem >= TC_CG ? 4 : (crem + 15) >> 4;
-          // one elected lane issues the whole stage: lean loop, descriptors as 32-bit lo words
+          // One elected lane issues the whole stage (all taps) from inside a single elect region, so nothing but the
+          // weight-stage waits separates the MMAs of consecutive taps (an elect / __syncwarp / descriptor rebuild per
+          // tap left the tensor pipe idle ~400 clk per tap).  The ring state that outlives the region (sbr, pb, bres16,
+          // acc) is advanced by ALL lanes after it, from uniform values: state mutated inside the region and carried
+          // around the loop would be lane-private, and descriptors built from it are moved to uniform registers by
+          // per-lane "waterfall" loops (~120 clk per MMA).
+          const uint32_t ahi = (uint32_t)(descA0 >> 32), bhi = (uint32_t)(descB0 >> 32);
+          const uint32_t rowlo0 = (uint32_t)descA0 + smA16 + sa * a_stage16;
+          const uint32_t blo0 = (uint32_t)descB0;
           if (elect_one()) {
-            const uint32_t ahi = (uint32_t)(descA0 >> 32), bhi = (uint32_t)(descB0 >> 32);
-            uint32_t rowlo = (uint32_t)descA0 + smA16 + sa * a_stage16;
-            const uint32_t blo0 = (uint32_t)descB0;
+            uint32_t s_ = sbr, p_ = pb, bres_ = bres16, acc_ = acc, rowlo = rowlo0;
             for (uint32_t ky = 0; ky < kh; ++ky, rowlo += PW * 8u) {
               uint32_t alo = rowlo;
               for (uint32_t kx = 0; kx < kw; ++kx, alo += 8u) {
                 uint32_t blo;
                 if (resident) {
-                  blo = blo0 + bres16;
-                  bres16 += b_stage16;
+                  blo = blo0 + bres_;
+                  bres_ += b_stage16;
                 } else {
-                  mbar_wait(fullB(sbr), pb);
+                  mbar_wait(fullB(s_), p_);
                   tc_fence_after();
-                  blo = blo0 + smB16 + sbr * b_stage16;
+                  blo = blo0 + smB16 + s_ * b_stage16;
                 }
                 if (nks == 4) {
 #pragma unroll
                   for (uint32_t ks = 0; ks < 4; ++ks) {
                     if (SPLIT == 3) {
-                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc2, ks == 0 ? acc : 1u);
+                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc2, ks == 0 ? acc_ : 1u);
                       tc_mma_bf16_lh(tmem_d, alo + 2 * ks + apart16, ahi, blo + 2 * ks, bhi, idesc, 1);
                     } else {
-                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc, ks == 0 ? acc : 1u);
+                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc, ks == 0 ? acc_ : 1u);
                     }
                   }
                 } else {
                   for (int ks = 0; ks < nks; ++ks) {
                     if (SPLIT == 3) {
-                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc2, ks == 0 ? acc : 1u);
+                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc2, ks == 0 ? acc_ : 1u);
                       tc_mma_bf16_lh(tmem_d, alo + 2 * ks + apart16, ahi, blo + 2 * ks, bhi, idesc, 1);
                     } else {
-                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc, ks == 0 ? acc : 1u);
+                      tc_mma_bf16_lh(tmem_d, alo + 2 * ks, ahi, blo + 2 * ks, bhi, idesc, ks == 0 ? acc_ : 1u);
                     }
                   }
                 }
-                acc = 1;
+                acc_ = 1;
                 if (!resident) {
-                  tc_commit(emptyB(sbr));
-                  if (++sbr == (uint32_t)NB) { sbr = 0; pb ^= 1; }
+                  tc_commit(emptyB(s_));
+                  if (++s_ == (uint32_t)NB) { s_ = 0; p_ ^= 1; }
                 }
               }
             }
+            tc_commit(emptyA(sa));
           }
-          // (acc, bres16, sbr, pb live in the elected lane only: elect.sync always picks the same lane)
           __syncwarp();
-          if (elect_one()) tc_commit(emptyA(sa));
-          __syncwarp();
+          // advance the carried state on every lane
+          acc = 1;
+          if (resident) {
+            bres16 += (uint32_t)ntaps * b_stage16;
+          } else {
+            sbr += (uint32_t)ntaps;
+            while (sbr >= (uint32_t)NB) { sbr -= (uint32_t)NB; pb ^= 1; }
+          }
           if (lane == 0) trace(lt * ngroups + gi, 2);
           if (++sa == (uint32_t)NA) { sa = 0; pa ^= 1; }
         }
@@ -466,12 +479,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
     __syncwarp();
   } else {
     // ===================== producers: fp32 patch -> bf16 hi/lo canonical smem =====================
-    // Group pg owns A stages ia = pg, pg+2, ...  The global loads of a stage are issued BEFORE
+    // All 256 producer threads fill every A stage together (16 patch pixels per pass, up to 192 pixels =
+    // a whole 3x3 / 1x5 / 5x1 patch in ONE batch of loads).  The global loads of a stage are issued BEFORE
     // waiting for its ring slot (they only need registers), so the HBM/L2 latency overlaps the
     // wait for the MMAs that free the slot.
-    const int pg = (warp - TC_W_PROD) >> 2;                      // producer group 0 / 1
-    const int tid = threadIdx.x - TC_W_PROD * 32 - pg * 128;     // 0..127 within the group
-    const int q = tid & 15, pl = tid >> 4;          // 16 float4 pieces per pixel, 8 pixels per pass
+    const int tid = threadIdx.x - TC_W_PROD * 32;                // 0..255
+    const int q = tid & 15, pl = tid >> 4;          // 16 float4 pieces per pixel, 16 pixels per pass
     const int P = g.P, PW = g.PW;
     const int py0 = pl / PW, px0 = pl - py0 * PW;
     const int ntl = S > (int)blockIdx.x ? (S - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
@@ -501,19 +514,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
     auto load_batch = [&](float4 (&v)[TC_PB], int p0, int& py, int& px) {
 #pragma unroll
       for (int u = 0; u < TC_PB; ++u) {
-        const int p = p0 + 8 * u;
+        const int p = p0 + 16 * u;
         const int iy = iy0 + py, ix = ix0 + px;
         v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (cvalid && p < P && iy >= 0 && iy < d.H && ix >= 0 && ix < d.W)
           v[u] = __ldg(reinterpret_cast<const float4*>(src + (img_pix + (int64_t)iy * d.W + ix) * cs));
-        px += 8;
+        px += 16;
         while (px >= PW) { px -= PW; ++py; }
       }
     };
     auto store_batch = [&](const float4 (&v)[TC_PB], int p0, uint8_t* dst_hi) {
 #pragma unroll
       for (int u = 0; u < TC_PB; ++u) {
-        const int p = p0 + 8 * u;
+        const int p = p0 + 16 * u;
         if (p < P) {
           uint2 hi, lo;
           split4(v[u], hi, lo);
@@ -527,11 +540,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
 
     float4 v[TC_PB];
     int py = py0, px = px0;
-    uint32_t ia = pg;
-    TcTracer trace(g, TC_W_PROD + pg);
+    uint32_t ia = 0;
+    TcTracer trace(g, TC_W_PROD);
     if (g.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
     if (ia < nia) { setup(ia); load_batch(v, pl, py, px); }
-    for (; ia < nia; ia += 2) {
+    for (; ia < nia; ++ia) {
       const uint32_t sa = ia % (uint32_t)NA, pa = ((ia / (uint32_t)NA) & 1) ^ 1;
       if (tid == 0) trace(ia, 0);
       mbar_wait(emptyA(sa), pa);
@@ -539,15 +552,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
       uint8_t* dst_hi = smA + sa * a_stage;
       store_batch(v, pl, dst_hi);
       if (tid == 0) trace(ia, 2);
-      for (int p0 = pl + 8 * TC_PB; p0 < P; p0 += 8 * TC_PB) {   // rest of the patch (96 pixels per batch)
+      for (int p0 = pl + 16 * TC_PB; p0 < P; p0 += 16 * TC_PB) {   // rest of a large patch (192 pixels per batch)
         load_batch(v, p0, py, px);
         store_batch(v, p0, dst_hi);
       }
+      // one arrival per warp: 256 per-thread arrivals on one mbarrier word serialise (~1 us per stage)
       fence_async_smem();
-      mbar_arrive(fullA(sa));
+      __syncwarp();
+      if (lane == 0) mbar_arrive(fullA(sa));
       if (tid == 0) trace(ia, 3);
-      if (ia + 2 < nia) {          // prefetch the next stage of this group into registers
-        setup(ia + 2);
+      if (ia + 1 < nia) {          // prefetch the next stage into registers
+        setup(ia + 1);
         py = py0; px = px0;
         load_batch(v, pl, py, px);
       }
@@ -661,12 +676,18 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
   const int npart = split == 3 ? 2 : 1;
   const size_t a_stage = (size_t)g.a_part * npart;
   const size_t b_stage = (size_t)BN * 128 * npart;
-  const size_t budget = 226 * 1024 - TC_BAR_BYTES - TC_EPI_BYTES;
   const size_t nstage = (size_t)g.ngroups * g.ntaps;
   const int n_tiles = ceil_div(d.cout, BN);
   int gx = kNumSMs / n_tiles;
   if (gx < 1) gx = 1;
   if (gx > g.S) gx = g.S;
+  // A CTA that owns a single pixel tile (the RAFT update block: 29 tiles) never refills its A ring after the last
+  // MMA, so the epilogue staging tile can live on top of it; the 36 KB go to the weight ring, whose depth bounds
+  // those kernels (each CTA streams all weights of its N tile once: bytes in flight / L2 round trip).
+  const bool alias = g.S <= gx && 2 * a_stage >= (size_t)TC_EPI_BYTES;
+  const size_t budget = 226 * 1024 - TC_BAR_BYTES - (alias ? 0 : TC_EPI_BYTES);
+  g.a_off = TC_BAR_BYTES + (alias ? 0 : TC_EPI_BYTES);
+  g.epi_off = TC_BAR_BYTES;
   // resident weights pay off when a CTA walks more than one pixel tile
   g.resident = (nstage * b_stage + 2 * a_stage <= budget && g.S > gx) ? 1 : 0;
   if (g.resident) {
@@ -675,6 +696,7 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
   } else {
     g.NA = (int)(budget / 2 / a_stage);
     if (g.NA < 2) g.NA = 2;
+    if (alias && g.NA > 2) g.NA = 2;                               // single tile: the weight ring needs the room
     if ((size_t)g.NA * a_stage + 2 * b_stage > budget) g.NA = 1;   // huge patches (7x7 hi+lo): no overlap
   }
   if (g.NA > 8) g.NA = 8;
@@ -684,7 +706,8 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
     if (g.NB > 32) g.NB = 32;
     if ((size_t)g.NB > nstage && nstage >= 2) g.NB = (int)nstage;
   }
-  const size_t smem = TC_BAR_BYTES + TC_EPI_BYTES + (size_t)g.NA * a_stage + (size_t)g.NB * b_stage;
+  ZT_REQUIRE(!alias || (size_t)g.NA * a_stage >= (size_t)TC_EPI_BYTES, "conv_tc: staging alias does not fit the A ring");
+  const size_t smem = (size_t)g.a_off + (size_t)g.NA * a_stage + (size_t)g.NB * b_stage;
   ZT_REQUIRE(smem <= 227 * 1024, "conv_tc: tile needs %zu B of shared memory", smem);
 
   dim3 grid(gx, n_tiles, 1);
