@@ -194,6 +194,10 @@ int zt_raft_convf1_f32(const float* flow, int f_cs, const float* weight, const f
 /* FlowHead.conv2 (model/RAFT/update.py:13-14): 3x3, C -> 2, no activation; weight fp32 [9][C][2] */
 int zt_conv3x3_n2_f32(const float* in, int in_cs, int C, const float* weight, const float* bias, float* out,
                       int out_cs, int H, int W, void* stream);
+/* FlowHead.conv2 fused with the per-iteration flow update (update.py:13-14 + raft.py:117-118): coords1 [H*W][2] +=
+ * conv3x3(in); flow = coords1 - pixel grid is written to f1 / f2 (NHWC, first 2 channels; either may be NULL) */
+int zt_flow_head2_update_f32(const float* in, int in_cs, int C, const float* weight, const float* bias,
+                             float* coords1, float* f1, int f1_cs, float* f2, int f2_cs, int H, int W, void* stream);
 
 /* ---- training path: Network.forward (model/model.py:144-203) and loss.py -------------------
  * NCHW fp32, batch 1.  Reduction entry points ADD raw sums into fp64 accumulators the caller

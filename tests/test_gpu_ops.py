@@ -434,3 +434,26 @@ def test_raft_small_kernels_vs_torch():
     d = torch.zeros(H * W, 4, device="cuda")
     ops.conv3x3_n2(xn, 256, 256, w2.permute(2, 3, 1, 0).reshape(9, 256, 2).contiguous(), b2, d, 4, H, W)
     assert (d[:, :2] - ref2).abs().max().item() < 1e-4 and torch.all(d[:, 2:] == 0)
+
+
+def test_flow_head2_update_matches_separate_kernels(dev):
+    """FlowHead.conv2 fused with coords1 += delta and the two flow outputs == conv3x3_n2 followed by flow_update."""
+    from zero_tig_b200 import ops
+    g = torch.Generator().manual_seed(12)
+    H, W = 13, 19
+    N = H * W
+    xn = nhwc(torch.randn(1, 256, H, W, generator=g))
+    w9 = (torch.randn(9, 256, 2, generator=g) * 0.05).cuda().contiguous()
+    b2 = torch.randn(2, generator=g).cuda()
+    ys, xs = torch.meshgrid(torch.arange(H), torch.arange(W), indexing="ij")
+    c_a = (torch.stack([xs, ys], -1).float().reshape(N, 2) + torch.randn(N, 2, generator=g)).cuda().contiguous()
+    c_b = c_a.clone()
+    d = torch.zeros(N, 4, device=dev)
+    fa, fb = torch.zeros(N, 4, device=dev), torch.zeros(N, 4, device=dev)
+    ha, hb = torch.zeros(N, 384, device=dev), torch.zeros(N, 384, device=dev)
+    ops.conv3x3_n2(xn, 256, 256, w9, b2, d, 4, H, W)
+    ops.flow_update(c_a, d, 4, fa, 4, ha, 384, 382, H, W)
+    ops.flow_head2_update(xn, 256, 256, w9, b2, c_b, fb, 4, hb, 384, 382, H, W)
+    assert torch.equal(c_a, c_b) and torch.equal(fa, fb) and torch.equal(ha, hb)
+    assert ha[:, 382:].abs().sum().item() > 0
+

@@ -51,6 +51,7 @@ SIGNATURES = {
     "zt_space_to_depth2_f32": [P, I, I, I, I, I, P, P],
     "zt_raft_convf1_f32": [P, I, P, P, P, I, I, I, P],
     "zt_conv3x3_n2_f32": [P, I, I, P, P, P, I, I, I, P],
+    "zt_flow_head2_update_f32": [P, I, I, P, P, P, P, I, P, I, I, I, P],
     "zt_pack_tc_rows_f32": [P, I, I, I, I, P, P],
     "zt_instnorm_nhwc_f32": [P, I, P, I, P, I, P, I, I, I, F, I, I, P],
     "zt_transpose_f32": [P, I, I, I, P, I, P],

@@ -63,9 +63,13 @@ __global__ void __launch_bounds__(256) convf1_kernel(const float* __restrict__ f
 }
 
 // one warp per position: out[pos][0..1] = bias + sum_{tap, c} in[pos+tap][c] * w[tap][c][0..1];  w = [9][C][2]
+// coords1 != NULL fuses the flow update of the iteration (raft.py:117-118: coords1 += delta; flow = coords1 - coords0
+// written to up to two NHWC buffers) into the flow head, so delta never goes through memory.
 __global__ void __launch_bounds__(256) conv3x3_n2_kernel(const float* __restrict__ in, int in_cs, int C,
                                                          const float* __restrict__ w, const float* __restrict__ bias,
-                                                         float* __restrict__ out, int out_cs, int H, int W) {
+                                                         float* __restrict__ out, int out_cs, int H, int W,
+                                                         float* __restrict__ coords1, float* __restrict__ f1, int f1_cs,
+                                                         float* __restrict__ f2, int f2_cs) {
   pdl_enter();
   const int lane = threadIdx.x & 31;
   const int pos = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -93,8 +97,19 @@ __global__ void __launch_bounds__(256) conv3x3_n2_kernel(const float* __restrict
     a1 += __shfl_xor_sync(0xffffffffu, a1, o);
   }
   if (lane == 0) {
-    out[(int64_t)pos * out_cs] = a0 + bias[0];
-    out[(int64_t)pos * out_cs + 1] = a1 + bias[1];
+    const float d0 = a0 + bias[0], d1 = a1 + bias[1];
+    if (out) {
+      out[(int64_t)pos * out_cs] = d0;
+      out[(int64_t)pos * out_cs + 1] = d1;
+    }
+    if (coords1) {
+      const float c0 = coords1[2 * pos] + d0, c1 = coords1[2 * pos + 1] + d1;
+      coords1[2 * pos] = c0;
+      coords1[2 * pos + 1] = c1;
+      const float fx = c0 - (float)x, fy = c1 - (float)y;
+      if (f1) { f1[(int64_t)pos * f1_cs] = fx; f1[(int64_t)pos * f1_cs + 1] = fy; }
+      if (f2) { f2[(int64_t)pos * f2_cs] = fx; f2[(int64_t)pos * f2_cs + 1] = fy; }
+    }
   }
 }
 
@@ -127,6 +142,18 @@ extern "C" int zt_conv3x3_n2_f32(const float* in, int in_cs, int C, const float*
   ZT_REQUIRE(in && weight && bias && out && C > 0 && (C & 3) == 0 && (in_cs & 3) == 0 && in_cs >= C && out_cs >= 2 &&
              H > 0 && W > 0, "conv3x3_n2: bad args");
   ZT_CUDA(launch_pdl(conv3x3_n2_kernel, dim3(ceil_div(H * W, 8)), dim3(256), 0, (cudaStream_t)stream, in, in_cs, C, weight,
-                     bias, out, out_cs, H, W));
+                     bias, out, out_cs, H, W, (float*)nullptr, (float*)nullptr, 0, (float*)nullptr, 0));
+  return check_launch("conv3x3_n2_kernel");
+}
+/* FlowHead.conv2 + the flow update of one RAFT iteration (update.py:13-14, raft.py:117-118) in one launch:
+ * delta = conv3x3(in); coords1 [H*W][2] += delta; flow = coords1 - pixel grid -> f1 / f2 (NHWC, 2 channels, may be NULL) */
+extern "C" int zt_flow_head2_update_f32(const float* in, int in_cs, int C, const float* weight, const float* bias,
+                                        float* coords1, float* f1, int f1_cs, float* f2, int f2_cs, int H, int W,
+                                        void* stream) {
+  using namespace zt;
+  ZT_REQUIRE(in && weight && bias && coords1 && C > 0 && (C & 3) == 0 && (in_cs & 3) == 0 && in_cs >= C && H > 0 && W > 0 &&
+             (!f1 || f1_cs >= 2) && (!f2 || f2_cs >= 2), "flow_head2_update: bad args");
+  ZT_CUDA(launch_pdl(conv3x3_n2_kernel, dim3(ceil_div(H * W, 8)), dim3(256), 0, (cudaStream_t)stream, in, in_cs, C, weight,
+                     bias, (float*)nullptr, 0, H, W, coords1, f1, f1_cs, f2, f2_cs));
   return check_launch("conv3x3_n2_kernel");
 }

@@ -349,11 +349,12 @@ class RaftEngine:
                 ops.conv2d(w["gru.q" + s], rh, 128, 128, 1, h8, w8, hx, 384, in1=hx, in1_cs=384, c1=256,
                            in1_off=128, pad=pad, epi="gru_q", aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128, tc=T, bn=32)
             ops.conv2d(w["fh1"], hx, 384, 128, 1, h8, w8, fhid, 256, pad=(1, 1), act="relu", tc=TH, bn=64)
-            if TH:
-                ops.conv3x3_n2(fhid, 256, 256, w["fh2.raw"][0], w["fh2.raw"][1], delta, 4, h8, w8)
+            if TH:     # flow head conv2 + coords1 += delta + flow outputs in one launch
+                ops.flow_head2_update(fhid, 256, 256, w["fh2.raw"][0], w["fh2.raw"][1], coords1, flow4, 4, hx, 384, 382,
+                                      h8, w8)
             else:
                 ops.conv2d(w["fh2"], fhid, 256, 256, 1, h8, w8, delta, 4, pad=(1, 1), tc=TH)
-            ops.flow_update(coords1, delta, 4, flow4, 4, hx, 384, 382, h8, w8)
+                ops.flow_update(coords1, delta, 4, flow4, 4, hx, 384, 382, h8, w8)
         # convex upsampling mask only for the returned (last) prediction (raft.py:122-130, Q15)
         mh = ws.get("maskh", (N, 256))
         mask = ws.get("mask", (N, 576))

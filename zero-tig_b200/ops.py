@@ -205,6 +205,12 @@ def conv3x3_n2(x, x_cs, Cn, w, b, out, out_cs, H, W):
     check(lib().zt_conv3x3_n2_f32(_p(x), x_cs, Cn, _p(w), _p(b), _p(out), out_cs, H, W, _stream()), "conv3x3_n2")
 
 
+def flow_head2_update(x, x_cs, Cn, w, b, coords1, f1, f1_cs, f2, f2_cs, f2_off, H, W):
+    """FlowHead.conv2 + coords1 += delta + flow outputs in one launch (update.py:13-14, raft.py:117-118)."""
+    check(lib().zt_flow_head2_update_f32(_p(x), x_cs, Cn, _p(w), _p(b), _p(coords1), _p(f1), f1_cs, _p(f2, f2_off), f2_cs,
+                                         H, W, _stream()), "flow_head2_update")
+
+
 def instnorm(x, x_cs, out, out_cs, stats, B, HW, Cn, relu_inner, relu_outer=False, res=None, res_cs=0, eps=1e-5):
     check(lib().zt_instnorm_nhwc_f32(_p(x), x_cs, _p(out), out_cs, _p(res), res_cs, _p(stats), B, HW, Cn,
                                      eps, int(relu_inner), int(relu_outer), _stream()), "instnorm")
