@@ -56,6 +56,11 @@ class RaftEngine:
     TC_HEAD = _tc_mode("RAFT_HEAD", TC)    # flow head + mask head
     TC_CORR = _tc_mode("RAFT_CORR", 3 if TC else 0)   # all-pairs correlation volume
     CORR_FUSED = int(os.environ.get("ZT_CORR_FUSED", "1"))   # volume + pyramid in one kernel (corr_gemm.cu)
+    BN96 = int(os.environ.get("ZT_ENC_BN96", "1"))
+    # N tiles of the two K = 2304 layers of the motion encoder (measured: 48 / 32 instead of 64 put 120 instead of
+    # 90 / 60 CTAs on the K loop and change the iteration time by < 1 %: these launches are not K-loop bound)
+    BN_C2 = int(os.environ.get("ZT_BN_C2", "64"))
+    BN_ENC = int(os.environ.get("ZT_BN_ENC", "64"))
 
     def __init__(self, raft):
         self.raft = raft
@@ -151,6 +156,8 @@ class RaftEngine:
             ops.instnorm(y, 64, y, 64, stats, B, h * wd, 64, relu_inner=True)
         cin = 64
         for li, (cout, stride) in enumerate(((64, 1), (96, 2), (128, 2)), start=1):
+            # one N tile for the 96-channel layers (two tiles of 64 + 32 fetch the A operand twice: §3.7 of DESIGN.md)
+            bn_l = 96 if cout == 96 and self.BN96 else 64
             for bi in (0, 1):
                 s = stride if bi == 0 else 1
                 p = f"{enc}.layer{li}.{bi}"
@@ -161,17 +168,17 @@ class RaftEngine:
                     ys = buf(f"l{li}.s2d", ho, wo, 4 * cin)
                     ops.space_to_depth2(y, cin, cin, B, h, wd, ys)
                     ops.conv2d(w[p + ".conv1.s2d"], ys, 4 * cin, 4 * cin, B, ho, wo, t1, cout, pad=(1, 1),
-                               act="relu" if is_bn else "none", tc=T, bn=64, crop=(ho, wo))
+                               act="relu" if is_bn else "none", tc=T, bn=bn_l, crop=(ho, wo))
                 else:
                     ops.conv2d(w[p + ".conv1"], y, cin, cin, B, h, wd, t1, cout, stride=s, pad=(1, 1),
-                               act="relu" if is_bn else "none", tc=T if s == 1 else 0, bn=64)
+                               act="relu" if is_bn else "none", tc=T if s == 1 else 0, bn=bn_l)
                 if not is_bn:
                     ops.instnorm(t1, cout, t1, cout, stats, B, ho * wo, cout, relu_inner=True)
                 sc = y
                 if s != 1:
                     sc = buf(f"l{li}b{bi}.sc", ho, wo, cout)
                     if ys is not None:   # 1x1 stride 2 = 1x1 on block (0,0) of the space-to-depth tensor
-                        ops.conv2d(w[p + ".down"], ys, 4 * cin, cin, B, ho, wo, sc, cout, tc=T, bn=64)
+                        ops.conv2d(w[p + ".down"], ys, 4 * cin, cin, B, ho, wo, sc, cout, tc=T, bn=bn_l)
                     else:
                         ops.conv2d(w[p + ".down"], y, cin, cin, B, h, wd, sc, cout, stride=s, pad=(0, 0))
                     if not is_bn:
@@ -179,10 +186,10 @@ class RaftEngine:
                 out = buf(f"l{li}b{bi}.out", ho, wo, cout)
                 if is_bn:
                     ops.conv2d(w[p + ".conv2"], t1, cout, cout, B, ho, wo, out, cout, pad=(1, 1), act="relu",
-                               epi="add_relu", aux0=sc, aux0_cs=cout, tc=T, bn=64)
+                               epi="add_relu", aux0=sc, aux0_cs=cout, tc=T, bn=bn_l)
                 else:
                     t2 = buf(f"l{li}b{bi}.t2", ho, wo, cout)
-                    ops.conv2d(w[p + ".conv2"], t1, cout, cout, B, ho, wo, t2, cout, pad=(1, 1), tc=T, bn=64)
+                    ops.conv2d(w[p + ".conv2"], t1, cout, cout, B, ho, wo, t2, cout, pad=(1, 1), tc=T, bn=bn_l)
                     ops.instnorm(t2, cout, out, cout, stats, B, ho * wo, cout, relu_inner=True, relu_outer=True,
                                  res=sc, res_cs=cout)
                 y, cin, h, wd = out, cout, ho, wo
@@ -332,9 +339,10 @@ class RaftEngine:
                            bn=32)
             ops.corr_lookup(lv, hs, wsz, coords1, corr, 324, N)   # correlation branch (update.py:90-91)
             ops.conv2d(w["enc.convc1"], corr, 324, 324, 1, h8, w8, c1, 256, act="relu", tc=T, bn=64)
-            ops.conv2d(w["enc.convc2"], c1, 256, 256, 1, h8, w8, c2f, 256, pad=(1, 1), act="relu", tc=T, bn=64)
+            ops.conv2d(w["enc.convc2"], c1, 256, 256, 1, h8, w8, c2f, 256, pad=(1, 1), act="relu", tc=T, bn=self.BN_C2)
             join()
-            ops.conv2d(w["enc.conv"], c2f, 256, 256, 1, h8, w8, hx, 384, out_off=256, pad=(1, 1), act="relu", tc=T, bn=64)
+            ops.conv2d(w["enc.conv"], c2f, 256, 256, 1, h8, w8, hx, 384, out_off=256, pad=(1, 1), act="relu", tc=T,
+                       bn=self.BN_ENC)
             for s, pad in (("1", (0, 2)), ("2", (2, 0))):
                 if T:
                     ops.conv2d(w[f"gru.zr{s}.hm"], hx, 384, 128, 1, h8, w8, rh, 128, in1=hx, in1_cs=384, c1=128,
