@@ -80,3 +80,17 @@ def test_pack_nhwc_bf16():
     ops.pack_nhwc_bf16([a], 3, 1e-4, out8, 8, 13 * 17)
     assert torch.equal(out8[:, :3], (a + 1e-4)[0].permute(1, 2, 0).reshape(-1, 3).to(torch.bfloat16))
     assert torch.all(out8[:, 3:] == 0)
+
+
+@pytest.mark.parametrize("nsrc,cs", [(1, 8), (2, 8), (3, 16), (4, 16)])
+def test_pack_nhwc_bf16_four_pixel_path(nsrc, cs):
+    """H*W % 4 == 0 takes the float4 / four-pixels-per-thread kernel; same result as the reference cat + permute."""
+    from zero_tig_b200 import ops
+    g = torch.Generator().manual_seed(2 + nsrc)
+    H, W = 24, 52
+    srcs = [torch.rand(1, 3, H, W, generator=g).cuda() for _ in range(nsrc)]
+    out = torch.full((H * W, cs), 7.0, dtype=torch.bfloat16, device="cuda")
+    ops.pack_nhwc_bf16(srcs, 3, 1e-4, out, cs, H * W)
+    want = (torch.cat(srcs, 1) + 1e-4)[0].permute(1, 2, 0).reshape(-1, 3 * nsrc).to(torch.bfloat16)
+    assert torch.equal(out[:, :3 * nsrc], want) and torch.all(out[:, 3 * nsrc:] == 0)
+

@@ -274,6 +274,42 @@ __global__ void __launch_bounds__(256) pack_nhwc_bf16_kernel(const float* __rest
   }
 }
 
+// fast path: three channels per source, four consecutive pixels per thread (float4 plane loads, 4*CS*2 contiguous
+// bytes written per thread), channel placement resolved at compile time
+template <int CS, int NSRC>
+__global__ void __launch_bounds__(256) pack_nhwc_bf16_x4_kernel(const float* __restrict__ s0, const float* __restrict__ s1,
+                                                                const float* __restrict__ s2, const float* __restrict__ s3,
+                                                                float add, __nv_bfloat16* __restrict__ out, int64_t HW) {
+  pdl_enter();
+  const float* src[4] = {s0, s1, s2, s3};
+  const int64_t n4 = HW >> 2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 v[NSRC * 3];
+#pragma unroll
+    for (int s = 0; s < NSRC; ++s)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) v[s * 3 + c] = __ldg(reinterpret_cast<const float4*>(src[s] + c * HW) + i);
+    uint4* o = reinterpret_cast<uint4*>(out + i * 4 * CS);
+#pragma unroll
+    for (int px = 0; px < 4; ++px) {
+      float r[CS];
+#pragma unroll
+      for (int c = 0; c < CS; ++c) {
+        if (c < NSRC * 3) {
+          const float4 t = v[c];
+          r[c] = (px == 0 ? t.x : px == 1 ? t.y : px == 2 ? t.z : t.w) + add;
+        } else {
+          r[c] = 0.f;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < CS / 8; ++j)
+        o[px * (CS / 8) + j] = make_uint4(pack_bf16x2(r[8 * j], r[8 * j + 1]), pack_bf16x2(r[8 * j + 2], r[8 * j + 3]),
+                                          pack_bf16x2(r[8 * j + 4], r[8 * j + 5]), pack_bf16x2(r[8 * j + 6], r[8 * j + 7]));
+    }
+  }
+}
+
 // ---- host: tensor-map cache ----
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -325,6 +361,19 @@ extern "C" int zt_pack_nhwc_bf16(const float* s0, const float* s1, const float* 
   ZT_REQUIRE(s0 && out && nsrc >= 1 && nsrc <= 4 && c_each >= 1 && c_each * nsrc <= cs && HW > 0, "pack_nhwc_bf16: bad args");
   ZT_REQUIRE((nsrc < 2 || s1) && (nsrc < 3 || s2) && (nsrc < 4 || s3), "pack_nhwc_bf16: missing source");
   ZT_REQUIRE(cs == 8 || cs == 16, "pack_nhwc_bf16: cs must be 8 or 16 (got %d)", cs);
+  const bool al16 = (((uintptr_t)s0 | (uintptr_t)s1 | (uintptr_t)s2 | (uintptr_t)s3) & 15) == 0;
+  if (c_each == 3 && (HW & 3) == 0 && al16 && nsrc * 3 <= cs) {
+    const int b4 = (int)std::min<int64_t>(ceil_div64(HW >> 2, 256), 8 * kNumSMs);
+    cudaStream_t st = (cudaStream_t)stream;
+    __nv_bfloat16* o = (__nv_bfloat16*)out;
+    cudaError_t e = cudaErrorInvalidValue;
+    if (cs == 8 && nsrc == 1) e = launch_pdl(pack_nhwc_bf16_x4_kernel<8, 1>, dim3(b4), dim3(256), 0, st, s0, s1, s2, s3, add, o, HW);
+    else if (cs == 8 && nsrc == 2) e = launch_pdl(pack_nhwc_bf16_x4_kernel<8, 2>, dim3(b4), dim3(256), 0, st, s0, s1, s2, s3, add, o, HW);
+    else if (cs == 16 && nsrc == 3) e = launch_pdl(pack_nhwc_bf16_x4_kernel<16, 3>, dim3(b4), dim3(256), 0, st, s0, s1, s2, s3, add, o, HW);
+    else if (cs == 16 && nsrc == 4) e = launch_pdl(pack_nhwc_bf16_x4_kernel<16, 4>, dim3(b4), dim3(256), 0, st, s0, s1, s2, s3, add, o, HW);
+    if (e == cudaSuccess) return check_launch("pack_nhwc_bf16_x4_kernel");
+    (void)cudaGetLastError();      // combination without a fast path: generic kernel below
+  }
   const int blocks = (int)std::min<int64_t>(ceil_div64(HW, 256), 16 * kNumSMs);
   if (cs == 8)
     pack_nhwc_bf16_kernel<8><<<blocks, 256, 0, (cudaStream_t)stream>>>(s0, s1, s2, s3, c_each, nsrc, add,
