@@ -42,40 +42,55 @@ struct LookupArgs {
   int h[4], w[4];
 };
 
-// One CTA (128 threads) per query position.  Per level the 10x10 window of the position's
-// own correlation plane that covers the 9x9 bilinear taps is staged in shared memory with
-// zeros outside the plane (grid_sample padding_mode='zeros'); then 324 outputs are written
-// contiguously (channel-fastest NHWC, the layout convc1 consumes).
+// One WARP per query position (4 queries per 128-thread CTA, no block-wide barrier): per level the 10x10
+// window of the position's own correlation plane that covers the 9x9 bilinear taps is staged in shared memory
+// with zeros outside the plane (grid_sample padding_mode='zeros') - 12-13 independent loads in flight per lane -
+// then 324 outputs are written contiguously (channel-fastest NHWC, the layout convc1 consumes).
 __global__ void __launch_bounds__(128) corr_lookup_kernel(const LookupArgs a, const float* __restrict__ coords,
-                                                          float* __restrict__ out, int out_cs) {
-  __shared__ float win[4][10][12];
-  __shared__ float frac[4][2];
+                                                          float* __restrict__ out, int out_cs, int N) {
+  __shared__ float win_s[4][4][10][12];
+  __shared__ float frac_s[4][4][2];
   pdl_enter();
-  const int n = blockIdx.x;
+  const int wq = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = blockIdx.x * 4 + wq;
+  if (n >= N) return;
+  float (*win)[10][12] = win_s[wq];
+  float (*frac)[2] = frac_s[wq];
   const float cx = coords[2 * n], cy = coords[2 * n + 1];
-  for (int i = threadIdx.x; i < 400; i += 128) {
-    const int l = i / 100, r = i - l * 100;
-    const int wy = r / 10, wx = r - wy * 10;
-    const float s = 1.f / (float)(1 << l);
-    const float x = cx * s, y = cy * s;      // coords / 2**i  (exact: power-of-two divide)
-    const float fx0 = floorf(x), fy0 = floorf(y);
-    const int ix = (int)fx0 - 4 + wx, iy = (int)fy0 - 4 + wy;
-    float v = 0.f;
-    if (ix >= 0 && ix < a.w[l] && iy >= 0 && iy < a.h[l])
-      v = __ldg(a.lvl[l] + ((int64_t)n * a.h[l] + iy) * a.w[l] + ix);
-    win[l][wy][wx] = v;
-    if (r == 0) { frac[l][0] = x - fx0; frac[l][1] = y - fy0; }
+#pragma unroll
+  for (int k = 0; k < 13; ++k) {
+    const int i = lane + 32 * k;
+    if (i < 400) {
+      const int l = i / 100, r = i - l * 100;
+      const int wy = r / 10, wx = r - wy * 10;
+      const float s = 1.f / (float)(1 << l);
+      const float x = cx * s, y = cy * s;      // coords / 2**i  (exact: power-of-two divide)
+      const float fx0 = floorf(x), fy0 = floorf(y);
+      const int ix = (int)fx0 - 4 + wx, iy = (int)fy0 - 4 + wy;
+      // selects instead of dynamic indexing: keeps the kernel parameters out of local memory
+      const int hl = l == 0 ? a.h[0] : l == 1 ? a.h[1] : l == 2 ? a.h[2] : a.h[3];
+      const int wl = l == 0 ? a.w[0] : l == 1 ? a.w[1] : l == 2 ? a.w[2] : a.w[3];
+      const float* pl = l == 0 ? a.lvl[0] : l == 1 ? a.lvl[1] : l == 2 ? a.lvl[2] : a.lvl[3];
+      float v = 0.f;
+      if (ix >= 0 && ix < wl && iy >= 0 && iy < hl) v = __ldg(pl + ((int64_t)n * hl + iy) * wl + ix);
+      win[l][wy][wx] = v;
+      if (r == 0) { frac[l][0] = x - fx0; frac[l][1] = y - fy0; }
+    }
   }
-  __syncthreads();
+  __syncwarp();
   float* o = out + (int64_t)n * out_cs;
-  for (int i = threadIdx.x; i < 324; i += 128) {
-    const int l = i / 81, r = i - l * 81;
-    const int ax = r / 9, by = r - ax * 9;   // channel = l*81 + a*9 + b : x-offset a, y-offset b (Q1)
-    const float fx = frac[l][0], fy = frac[l][1];
-    const float v00 = win[l][by][ax], v01 = win[l][by][ax + 1];
-    const float v10 = win[l][by + 1][ax], v11 = win[l][by + 1][ax + 1];
-    // grid_sample bilinear: nw*(1-fx)(1-fy) + ne*fx(1-fy) + sw*(1-fx)fy + se*fx*fy
-    o[i] = v00 * ((1.f - fx) * (1.f - fy)) + v01 * (fx * (1.f - fy)) + v10 * ((1.f - fx) * fy) + v11 * (fx * fy);
+#pragma unroll
+  for (int k = 0; k < 11; ++k) {
+    const int i = lane + 32 * k;
+    if (i < 324) {
+      const int l = i / 81, r = i - l * 81;
+      const int ax = r / 9, by = r - ax * 9;   // channel = l*81 + a*9 + b : x-offset a, y-offset b (Q1)
+      const float fx = frac[l][0], fy = frac[l][1];
+      const float v00 = win[l][by][ax], v01 = win[l][by][ax + 1];
+      const float v10 = win[l][by + 1][ax], v11 = win[l][by + 1][ax + 1];
+      // grid_sample bilinear: nw*(1-fx)(1-fy) + ne*fx(1-fy) + sw*(1-fx)fy + se*fx*fy
+      o[i] = v00 * ((1.f - fx) * (1.f - fy)) + v01 * (fx * (1.f - fy)) + v10 * ((1.f - fx) * fy) + v11 * (fx * fy);
+    }
   }
 }
 
@@ -165,7 +180,7 @@ extern "C" int zt_corr_lookup_f32(const float* l0, const float* l1, const float*
     // the reference divides by (W-1), (H-1): a 1-pixel level is NaN there; refuse.
     ZT_REQUIRE(hs[i] >= 2 && ws_[i] >= 2, "corr_lookup: pyramid level %d is %dx%d; the reference yields NaN below 2x2", i, hs[i], ws_[i]);
   }
-  ZT_CUDA(launch_pdl(corr_lookup_kernel, dim3(N), dim3(128), 0, (cudaStream_t)stream, a, coords, out, out_cs));
+  ZT_CUDA(launch_pdl(corr_lookup_kernel, dim3(ceil_div(N, 4)), dim3(128), 0, (cudaStream_t)stream, a, coords, out, out_cs, N));
   return check_launch("corr_lookup_kernel");
 }
 
