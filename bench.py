@@ -244,7 +244,7 @@ def run_b200(args):
     # ---- end to end through the public host-buffer API (FramePipeline: pinned host frames in, pinned host
     # H2/H3 out, every frame's H2D and D2H inside the timed region, overlapped with compute on side streams) ----
     from zero_tig_b200.pipeline import FramePipeline
-    pipe = FramePipeline(model, H, W, depth=2)
+    pipe = FramePipeline(model, H, W, depth=int(os.environ.get("ZT_PIPE_DEPTH", "2")))
     host_frames = [clip_host[frame(i):frame(i) + 1] for i in range(K)]
     sink = []
     pipe.run(host_frames[:min(Wm, 3)], lambda i, a, b: None, new_sequence=False)
