@@ -178,6 +178,10 @@ typedef struct ZtConvBf16 {
   void* out; int out_cs; int out_f32;
   const void* res; int res_cs;
   int H; int W; int cout; int kh; int kw; int act;
+  /* optional fused 1x1 head (the denoisers' last layer, model/model.py:27,43), head_n = 0: none.  Then out is fp32
+   * [H*W][out_cs] (out_cs 4 or 8 >= head_n) = head_b + head_w . act(conv + bias): head_w fp32 [8][64] (row = head
+   * channel, zero padded), head_b fp32 [8]; the cout-channel activation itself is not written. */
+  const float* head_w; const float* head_b; int head_n;
 } ZtConvBf16;
 int zt_conv2d_bf16_tma(const ZtConvBf16* desc, void* stream);
 /* NCHW fp32 planes (+add) -> bf16 NHWC [HW][cs], cs = 8 or 16, zero padded (virtual torch.cat, model.py:313,326,334) */

@@ -94,3 +94,44 @@ def test_pack_nhwc_bf16_four_pixel_path(nsrc, cs):
     want = (torch.cat(srcs, 1) + 1e-4)[0].permute(1, 2, 0).reshape(-1, 3 * nsrc).to(torch.bfloat16)
     assert torch.equal(out[:, :3 * nsrc], want) and torch.all(out[:, 3 * nsrc:] == 0)
 
+
+
+@pytest.mark.parametrize("hn,H,W", [(3, 37, 45), (6, 50, 70), (6, 16, 8), (3, 270, 480)])
+def test_conv_bf16_tma_fused_head(hn, H, W):
+    """conv2 (3x3, 48 -> 48, LeakyReLU) with conv3 (1x1, 48 -> 3 / 6) applied in its epilogue (model.py:26-27,42-43)
+    against torch on the same bf16-rounded conv2 operands.  The 48-channel activation stays in fp32 registers, so the
+    result is compared with the fp32 chain (tighter than the two-launch path, which rounds it to bf16 in between)."""
+    from zero_tig_b200 import ops
+    g = torch.Generator().manual_seed(100 + hn)
+    x = torch.randn(1, 48, H, W, generator=g).cuda()
+    w2 = (torch.randn(48, 48, 3, 3, generator=g) * (1.5 / (48 * 9) ** 0.5)).cuda()
+    b2 = (torch.randn(48, generator=g) * 0.1).cuda()
+    w3 = (torch.randn(hn, 48, 1, 1, generator=g) * (1.5 / 48 ** 0.5)).cuda()
+    b3 = (torch.randn(hn, generator=g) * 0.1).cuda()
+    xb, w2b = x.to(torch.bfloat16).float(), w2.to(torch.bfloat16).float()
+    mid = F.leaky_relu(F.conv2d(xb.double(), w2b.double(), b2.double(), padding=1), 0.2)
+    want = F.conv2d(mid, w3.double(), b3.double())[0].permute(1, 2, 0).reshape(H * W, hn).float()
+    xn = _nhwc_bf16(x, 48)
+    ocs = 4 if hn <= 4 else 8
+    out = torch.full((H * W, ocs), 7.0, device="cuda")
+    ops.conv2d_bf16(ops.ConvW(w2, b2, cin_pad=48), xn, 48, H, W, out, ocs, act="lrelu", head=ops.ConvW(w3, b3))
+    torch.cuda.synchronize()
+    assert torch.all(out[:, hn:] == 0)
+    err = (out[:, :hn] - want).abs().max().item()
+    assert err <= 3e-5 * max(1.0, want.abs().max().item()), err
+    # and the two-launch path agrees to its bf16 intermediate rounding
+    a2 = torch.zeros(H * W, 48, dtype=torch.bfloat16, device="cuda")
+    out2 = torch.zeros(H * W, ocs, device="cuda")
+    ops.conv2d_bf16(ops.ConvW(w2, b2, cin_pad=48), xn, 48, H, W, a2, 48, act="lrelu")
+    ops.conv2d_bf16(ops.ConvW(w3, b3, cin_pad=48), a2, 48, H, W, out2, ocs, out_f32=True)
+    assert (out - out2).abs().max().item() < 0.05
+
+
+def test_conv_bf16_tma_fused_head_bad_args():
+    from zero_tig_b200 import ops
+    x = torch.zeros(64, 48, dtype=torch.bfloat16, device="cuda")
+    w2 = ops.ConvW(torch.zeros(48, 48, 3, 3, device="cuda"), torch.zeros(48, device="cuda"), cin_pad=48)
+    w3 = ops.ConvW(torch.zeros(6, 48, 1, 1, device="cuda"), torch.zeros(6, device="cuda"))
+    out = torch.zeros(64, 4, device="cuda")
+    with pytest.raises(RuntimeError, match="fused head"):
+        ops.conv2d_bf16(w2, x, 48, 8, 8, out, 4, act="lrelu", head=w3)      # 6 head channels into a 4-wide row

@@ -35,6 +35,7 @@ class ZtConvBf16(C.Structure):
         ("out", c_fp), ("out_cs", C.c_int), ("out_f32", C.c_int),
         ("res", c_fp), ("res_cs", C.c_int),
         ("H", C.c_int), ("W", C.c_int), ("cout", C.c_int), ("kh", C.c_int), ("kw", C.c_int), ("act", C.c_int),
+        ("head_w", c_fp), ("head_b", c_fp), ("head_n", C.c_int),
     ]
 
 

@@ -42,6 +42,8 @@ struct TmArgs {
   const __nv_bfloat16* res;
   int res_cs;
   int H, W, cout, ph, pw;
+  const float* head_w;                    // OUT = 3: fp32 [8][64] weights of a fused 1x1 head (zero padded), bias [8]
+  const float* head_b;
 };
 
 __device__ __forceinline__ float tm_act(float v, int act) {
@@ -55,7 +57,9 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   return *reinterpret_cast<const uint32_t*>(&h);
 }
 
-// OUT: 0 = bf16 out, 1 = bf16 out with residual (out = res + act(v)), 2 = fp32 out (cout <= 8)
+// OUT: 0 = bf16 out, 1 = bf16 out with residual (out = res + act(v)), 2 = fp32 out (cout <= 8),
+//      3 = fp32 out of a fused 1x1 head: out[h] = head_b[h] + sum_c head_w[h][c] * act(v[c] + bias[c]), h < out_cs
+//          (the 48 -> 3 / 48 -> 6 heads of the denoisers, model.py:27,43: the 48-channel activation never goes to HBM)
 template <int OUT, int ACT>
 __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_constant__ CUtensorMap tmap,
                                                                  const TmArgs a, const TmGeom g) {
@@ -82,6 +86,12 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
     mbar_init(fullW, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(accFull(s), 1); mbar_init(accEmpty(s), 256); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __shared__ __align__(16) float hw_s[OUT == 3 ? 8 * 64 : 4];
+  __shared__ __align__(16) float part_s[OUT == 3 ? 4 * 32 * 8 : 4];
+  if (OUT == 3) {
+    // constants, fetched before the dependency wait; stored channel-major so one channel's 8 weights are two LDS.128
+    for (int i = threadIdx.x; i < 8 * 64; i += TM_THREADS) hw_s[(i & 63) * 8 + (i >> 6)] = __ldg(a.head_w + i);
   }
   if (warp == TM_W_MMA) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
@@ -140,6 +150,42 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
       // the accumulator is in registers: hand the TMEM buffer back before the stores
       tc_fence_before();
       mbar_arrive(accEmpty(buf));
+      if (OUT == 3) {
+        // fused 1x1 head: partial dot products over this thread's <= 32 channels, the two channel halves of a pixel
+        // (warps q and q + 4, same lane) meet in shared memory under a 64-thread named barrier
+        float part[8];
+#pragma unroll
+        for (int h = 0; h < 8; ++h) part[h] = 0.f;
+        if (has_cols) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const float x = tm_act(__uint_as_float(v[i]) + bias[i], ACT);
+            const float4 w0 = *reinterpret_cast<const float4*>(hw_s + (c0 + i) * 8);
+            const float4 w1 = *reinterpret_cast<const float4*>(hw_s + (c0 + i) * 8 + 4);
+            part[0] = fmaf(x, w0.x, part[0]); part[1] = fmaf(x, w0.y, part[1]);
+            part[2] = fmaf(x, w0.z, part[2]); part[3] = fmaf(x, w0.w, part[3]);
+            part[4] = fmaf(x, w1.x, part[4]); part[5] = fmaf(x, w1.y, part[5]);
+            part[6] = fmaf(x, w1.z, part[6]); part[7] = fmaf(x, w1.w, part[7]);
+          }
+        }
+        float* ps = part_s + (quad * 32 + lane) * 8;
+        if (half == 1) {
+          *reinterpret_cast<float4*>(ps) = make_float4(part[0], part[1], part[2], part[3]);
+          *reinterpret_cast<float4*>(ps + 4) = make_float4(part[4], part[5], part[6], part[7]);
+        }
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");
+        if (half == 0 && oy < a.H && ox < a.W) {
+          const float4 p0 = *reinterpret_cast<const float4*>(ps), p1 = *reinterpret_cast<const float4*>(ps + 4);
+          float* o = reinterpret_cast<float*>(a.out) + pix * a.out_cs;
+          *reinterpret_cast<float4*>(o) = make_float4(part[0] + p0.x + __ldg(a.head_b + 0), part[1] + p0.y + __ldg(a.head_b + 1),
+                                                      part[2] + p0.z + __ldg(a.head_b + 2), part[3] + p0.w + __ldg(a.head_b + 3));
+          if (a.out_cs > 4)
+            *reinterpret_cast<float4*>(o + 4) = make_float4(part[4] + p1.x + __ldg(a.head_b + 4), part[5] + p1.y + __ldg(a.head_b + 5),
+                                                            part[6] + p1.z + __ldg(a.head_b + 6), part[7] + p1.w + __ldg(a.head_b + 7));
+        }
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");     // part_s may be overwritten by the next tile
+        continue;
+      }
       if (!ok) continue;
       if (OUT == 2) {
         float* o = reinterpret_cast<float*>(a.out) + pix * a.out_cs;
@@ -395,7 +441,11 @@ extern "C" int zt_conv2d_bf16_tma(const ZtConvBf16* dp, void* stream) {
   ZT_REQUIRE(d.H > 0 && d.W > 0 && (int64_t)d.H * d.W < (1ll << 31), "conv_bf16_tma: bad dims");
   ZT_REQUIRE(((uintptr_t)d.in & 15) == 0 && ((uintptr_t)d.weight & 15) == 0 && ((uintptr_t)d.out & 15) == 0,
              "conv_bf16_tma: pointers must be 16-byte aligned");
-  if (d.out_f32) {
+  if (d.head_n) {
+    ZT_REQUIRE(d.head_n >= 1 && d.head_n <= 8 && d.head_w && d.head_b && d.out_f32 && !d.res &&
+                   (d.out_cs == 4 || d.out_cs == 8) && d.out_cs >= d.head_n,
+               "conv_bf16_tma: fused head needs head_n <= 8, fp32 output with out_cs 4 or 8, no residual");
+  } else if (d.out_f32) {
     ZT_REQUIRE(d.cout <= 8 && (d.out_cs == 4 || d.out_cs == 8) && d.out_cs >= d.cout && !d.res,
                "conv_bf16_tma: fp32 output needs cout <= 8, out_cs 4 or 8, no residual");
   } else {
@@ -415,7 +465,7 @@ extern "C" int zt_conv2d_bf16_tma(const ZtConvBf16* dp, void* stream) {
   g.w_bytes = g.w_tap * d.kh * d.kw;
   g.tmem_cols = 32;
   while (g.tmem_cols < 2 * g.BN) g.tmem_cols <<= 1;
-  const size_t budget = 226 * 1024 - TM_BAR_BYTES - g.w_bytes;
+  const size_t budget = 226 * 1024 - TM_BAR_BYTES - g.w_bytes - (d.head_n ? 6 * 1024 : 0);     // static smem of OUT = 3
   g.NA = (int)std::min<size_t>(4, budget / g.a_stage);
   ZT_REQUIRE(g.NA >= 2, "conv_bf16_tma: tile does not fit shared memory");
   const size_t smem = TM_BAR_BYTES + (size_t)g.NA * g.a_stage + g.w_bytes;
@@ -425,6 +475,7 @@ extern "C" int zt_conv2d_bf16_tma(const ZtConvBf16* dp, void* stream) {
   a.weight = (const uint8_t*)d.weight; a.bias = d.bias; a.out = d.out; a.out_cs = d.out_cs;
   a.res = (const __nv_bfloat16*)d.res; a.res_cs = d.res_cs;
   a.H = d.H; a.W = d.W; a.cout = d.cout; a.ph = d.kh / 2; a.pw = d.kw / 2;
+  a.head_w = d.head_w; a.head_b = d.head_b;
   const int gx = std::min(kNumSMs, g.S);
   cudaStream_t st = (cudaStream_t)stream;
 #define ZT_TM_LAUNCH(OUT, ACT)                                                                              \
@@ -432,13 +483,16 @@ extern "C" int zt_conv2d_bf16_tma(const ZtConvBf16* dp, void* stream) {
     static bool attr_done = false;                                                                          \
     if (!attr_done) {                                                                                       \
       ZT_CUDA(cudaFuncSetAttribute(conv_tma_kernel<OUT, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
-                                   227 * 1024));                                                            \
+                                   ((OUT) == 3 ? 220 : 227) * 1024));    /* OUT = 3 has 6 KB static */       \
       attr_done = true;                                                                                     \
     }                                                                                                       \
     ZT_CUDA(launch_pdl(conv_tma_kernel<OUT, ACT>, dim3(gx), dim3(TM_THREADS), smem, st, tmap, a, g));       \
     return check_launch("conv_tma_kernel");                                                                 \
   } while (0)
-  if (d.out_f32) {
+  if (d.head_n) {
+    if (d.act == ZT_ACT_LRELU02) ZT_TM_LAUNCH(3, ZT_ACT_LRELU02);
+    if (d.act == ZT_ACT_RELU) ZT_TM_LAUNCH(3, ZT_ACT_RELU);
+  } else if (d.out_f32) {
     if (d.act == ZT_ACT_NONE) ZT_TM_LAUNCH(2, ZT_ACT_NONE);
     if (d.act == ZT_ACT_SIGMOID) ZT_TM_LAUNCH(2, ZT_ACT_SIGMOID);
   } else if (d.res) {

@@ -407,6 +407,7 @@ class FrameEngine:
     TC_D1 = _tc_mode("D1", 2)
     TC_ENH = _tc_mode("ENH", 2)
     TC_D2 = _tc_mode("D2", 2)
+    HEAD_FUSED = int(os.environ.get("ZT_HEAD_FUSED", "1"))   # denoisers' 1x1 heads in the 3x3 layer's epilogue (conv_tma OUT = 3)
 
     def __init__(self, model):
         self.model = model
@@ -445,8 +446,11 @@ class FrameEngine:
             xp, a1, a2 = ws.get("xp8", (HW, 8), bf), ws.get("b48a", (HW, 48), bf), ws.get("b48b", (HW, 48), bf)
             ops.pack_nhwc_bf16([x], 3, self.EPS, xp, 8, HW)
             ops.conv2d_bf16(w["d1.c1"], xp, 8, H, W, a1, 48, act="lrelu")
-            ops.conv2d_bf16(w["d1.c2"], a1, 48, H, W, a2, 48, act="lrelu")
-            ops.conv2d_bf16(w["d1.c3"], a2, 48, H, W, d, 4, out_f32=True)
+            if self.HEAD_FUSED:    # conv3 (1x1, 48 -> 3) applied in conv2's epilogue: a2 is never written
+                ops.conv2d_bf16(w["d1.c2"], a1, 48, H, W, d, 4, act="lrelu", head=w["d1.c3"])
+            else:
+                ops.conv2d_bf16(w["d1.c2"], a1, 48, H, W, a2, 48, act="lrelu")
+                ops.conv2d_bf16(w["d1.c3"], a2, 48, H, W, d, 4, out_f32=True)
             L2 = torch.empty_like(x)
             ops.retinex_l2(x, d, 4, L2, HW, self.EPS)
             return L2
@@ -503,8 +507,11 @@ class FrameEngine:
             dp, a1, a2 = ws.get("dp16", (HW, 16), bf), ws.get("b48a", (HW, 48), bf), ws.get("b48b", (HW, 48), bf)
             ops.pack_nhwc_bf16([H3_wp, s3_wp, H2, s2], 3, 0.0, dp, 16, HW)
             ops.conv2d_bf16(w["d2.c1"], dp, 16, H, W, a1, 48, act="lrelu")
-            ops.conv2d_bf16(w["d2.c2"], a1, 48, H, W, a2, 48, act="lrelu")
-            ops.conv2d_bf16(w["d2.c3"], a2, 48, H, W, d, 8, out_f32=True)
+            if self.HEAD_FUSED:
+                ops.conv2d_bf16(w["d2.c2"], a1, 48, H, W, d, 8, act="lrelu", head=w["d2.c3"])
+            else:
+                ops.conv2d_bf16(w["d2.c2"], a1, 48, H, W, a2, 48, act="lrelu")
+                ops.conv2d_bf16(w["d2.c3"], a2, 48, H, W, d, 8, out_f32=True)
             H3 = torch.empty_like(H2)
             s3 = torch.empty_like(H2)
             ops.retinex_h5(H2, s2, d, 8, H3, s3, HW, self.EPS)

@@ -102,9 +102,33 @@ class ConvW:
         return t
 
 
-def conv2d_bf16(wt: ConvW, x, cin, H, W, out, out_cs, *, act="none", res=None, res_cs=0, out_f32=False):
-    """TMA-fed tcgen05 convolution over bf16 NHWC activations (csrc/conv_tma.cu): 3x3 pad 1 or 1x1."""
+    def head_pack(self):
+        """fp32 [8][64] weights + [8] bias of a 1x1 convolution fused into the preceding layer's epilogue
+        (csrc/conv_tma.cu, OUT = 3); rows / columns beyond cout / cin are zero."""
+        t = self._tc.get("head")
+        if t is None:
+            w = self.w_raw
+            cout, cin, kh, kw = w.shape
+            assert kh == 1 and kw == 1 and cout <= 8 and cin <= 64
+            hw = torch.zeros(8, 64, device=w.device, dtype=torch.float32)
+            hw[:cout, :cin] = w[:, :, 0, 0]
+            hb = torch.zeros(8, device=w.device, dtype=torch.float32)
+            if self.b_raw is not None:
+                hb[:cout] = self.b_raw
+            torch.cuda.current_stream().synchronize()   # fetched before griddepcontrol.wait (see tc_pack)
+            t = (hw, hb)
+            self._tc["head"] = t
+        return t
+
+
+def conv2d_bf16(wt: ConvW, x, cin, H, W, out, out_cs, *, act="none", res=None, res_cs=0, out_f32=False, head=None):
+    """TMA-fed tcgen05 convolution over bf16 NHWC activations (csrc/conv_tma.cu): 3x3 pad 1 or 1x1.
+    head = ConvW of a following 1x1 convolution (cout <= 8) applied in the epilogue: out is then its fp32 result."""
     d = ZtConvBf16()
+    if head is not None:
+        hw, hb = head.head_pack()
+        d.head_w, d.head_b, d.head_n = _p(hw), _p(hb), head.w_raw.shape[0]
+        out_f32 = True
     d.in_, d.cin = _p(x), cin
     d.weight, d.bias = _p(wt.tma_pack()), _p(wt.b_raw)
     d.out, d.out_cs, d.out_f32 = _p(out), out_cs, int(out_f32)
