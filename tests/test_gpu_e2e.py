@@ -145,3 +145,32 @@ def test_frame_pipeline_matches_direct_calls(model_factory, u8):
                 assert g_.shape == (H, W, 3) and np.array_equal(g_.numpy(), ref), t
             else:
                 assert torch.equal(g_, w_), t
+
+
+@pytest.mark.parametrize("H,W,dataset,n", [(1080, 1920, "RLV", 3), (2160, 3840, "underwater", 2)])
+def test_full_size_clip_vs_oracle(H, W, dataset, n, weights, tmp_path):
+    """BASELINE.json configs[1] (1080p RLV) and configs[3] (4K underwater, BVI-Coral-style `is_WB` weights) at their
+    full frame sizes, of_scale 3, against the CPU oracle on the same synthetic clip: every returned frame >= 50 dB,
+    last flow_up EPE <= 0.01 px.  The oracle needs ~2 s (1080p) / ~8 s (4K) per frame on the box's host cores."""
+    import zt_oracle as O
+    from zero_tig_b200 import synth, _lib
+    from zero_tig_b200.model.model import Finetunemodel
+    ck = tmp_path / "synthetic.pt"
+    torch.save(weights, ck)
+    m = Finetunemodel(synth.make_args(dataset=dataset, of_scale=3, model_pretrain=str(ck))).cuda().eval()
+    m.raft.load_state_dict({k[5:]: v for k, v in weights.items() if k.startswith("raft.")})
+    clip = synth.synthetic_clip(n, H, W, seed=3, underwater=(dataset == "underwater"))
+    st, tr = O.InferState(), {}
+    before = _lib.launch_count()
+    for t in range(n):
+        m.is_new_seq = (t == 0)
+        got = m(clip[t:t + 1].cuda())
+        ref = O.finetune_forward(clip[t:t + 1], weights, st, t == 0, 3, trace=tr)
+        for name, v, r in zip(("H2", "H3", "s3"), got, ref):
+            assert v.shape == (1, 3, H, W)
+            p = psnr(v.cpu(), r)
+            assert p >= PSNR_TOL, (name, t, p)
+    assert _lib.launch_count() - before > 100
+    fu = [v for k, v in m.raft.engine().ws.bufs.items() if k[0] == "flow_up"][0]
+    assert fu.shape == tr["flow_up"].shape
+    assert epe(fu.cpu(), tr["flow_up"]) <= EPE_TOL

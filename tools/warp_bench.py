@@ -4,7 +4,12 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from zero_tig_b200 import ops
 H, W, hf, wf = 1080, 1920, 360, 640
 g = torch.Generator().manual_seed(0)
-flow = (torch.randn(1, 2, hf, wf, generator=g) * 3).cuda()
+if os.environ.get("WARP_FLOW", "random") == "smooth":     # what RAFT returns on a real clip: ~1 px, slowly varying
+    yy, xx = torch.meshgrid(torch.arange(hf, dtype=torch.float32), torch.arange(wf, dtype=torch.float32), indexing="ij")
+    flow = torch.stack([0.7 + 0.5 * torch.sin(xx / 31.0) * torch.cos(yy / 47.0),
+                        0.35 + 0.4 * torch.cos(xx / 53.0 + yy / 29.0)])[None].contiguous().cuda()
+else:
+    flow = (torch.randn(1, 2, hf, wf, generator=g) * 3).cuda()
 sets = [(torch.rand(1, 3, H, W, generator=g).cuda(), torch.rand(1, 3, H, W, generator=g).cuda(),
          torch.empty(1, 3, H, W).cuda(), torch.empty(1, 3, H, W).cuda()) for _ in range(4)]   # 4 x 100 MB > L2
 for _ in range(3):
