@@ -45,19 +45,33 @@ struct CgPack {
   int h[4], w[4];
   int row0[4];           // first P row of level l
   int Npad, Ptot;
+  int64_t items[5];      // pack work items: [0, items[0]) Q rows; [items[l], items[l+1]) level l (level 0 starts at items[0])
 };
 
 // fmap [2N][fm_rs] fp32 -> Q hi/lo [Npad][256] bf16 (fmap1, zero rows beyond N) and
 // P hi/lo [Ptot][256] bf16 (level l rows row0[l].. in row-major (y_l, x_l) order = window means of fmap2)
-__global__ void corr_pack_kernel(const float* __restrict__ fmap, int fm_rs, const CgPack g,
-                                 __nv_bfloat16* __restrict__ Qhi, __nv_bfloat16* __restrict__ Qlo,
-                                 __nv_bfloat16* __restrict__ Phi, __nv_bfloat16* __restrict__ Plo) {
+__global__ void __launch_bounds__(256) corr_pack_kernel(const float* __restrict__ fmap, int fm_rs, const CgPack g,
+                                                        __nv_bfloat16* __restrict__ Qhi, __nv_bfloat16* __restrict__ Qlo,
+                                                        __nv_bfloat16* __restrict__ Phi, __nv_bfloat16* __restrict__ Plo) {
   pdl_enter();
   const int N = g.h[0] * g.w[0];
-  const int64_t total = (int64_t)(g.Npad + g.Ptot) * 64;      // one thread per 4 channels
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c4 = (int)(i & 63);
-    const int row = (int)(i >> 6);
+  // Work items: one per (row, 4 channels) for Q and level 0; for pooled level l the 2^l x 2^l window is split over
+  // 2^l adjacent lanes (lane = window row dy, each sums its 2^l values with all loads in flight) and folded with
+  // xor-shuffles - a single thread walking the 8x8 window (64 dependent-issue loads) was the long pole of this kernel.
+  // Segment sizes are multiples of 32 items, so a warp never straddles two levels.
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < g.items[4]; i += (int64_t)gridDim.x * blockDim.x) {
+    const int l = (i >= g.items[1]) + (i >= g.items[2]) + (i >= g.items[3]);
+    int64_t j = i;
+    int row, dy = 0;
+    if (i < g.items[0]) {                      // Q rows
+      row = (int)(j >> 6);
+    } else {
+      j -= (l == 0 ? g.items[0] : l == 1 ? g.items[1] : l == 2 ? g.items[2] : g.items[3]);
+      dy = (int)(j & ((1 << l) - 1));
+      j >>= l;
+      row = g.Npad + (l == 0 ? g.row0[0] : l == 1 ? g.row0[1] : l == 2 ? g.row0[2] : g.row0[3]) + (int)(j >> 6);
+    }
+    const int c4 = (int)(j & 63);
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     __nv_bfloat16 *dh, *dl;
     if (row < g.Npad) {
@@ -66,25 +80,32 @@ __global__ void corr_pack_kernel(const float* __restrict__ fmap, int fm_rs, cons
       dl = Qlo + (int64_t)row * 256 + c4 * 4;
     } else {
       const int r = row - g.Npad;
-      const int l = (r >= g.row0[1]) + (r >= g.row0[2]) + (r >= g.row0[3]);
-      const int m = r - g.row0[l];
-      if (m < g.h[l] * g.w[l]) {
-        const int y = m / g.w[l], x = m - y * g.w[l];
-        const int win = 1 << l;
-        const float* src = fmap + ((int64_t)N + (int64_t)(y * win) * g.w[0] + x * win) * fm_rs + c4 * 4;
+      const int hl = l == 0 ? g.h[0] : l == 1 ? g.h[1] : l == 2 ? g.h[2] : g.h[3];
+      const int wl = l == 0 ? g.w[0] : l == 1 ? g.w[1] : l == 2 ? g.w[2] : g.w[3];
+      const int m = r - (l == 0 ? g.row0[0] : l == 1 ? g.row0[1] : l == 2 ? g.row0[2] : g.row0[3]);
+      const int win = 1 << l;
+      if (m < hl * wl) {                       // uniform over the 2^l lanes of a window
+        const int y = m / wl, x = m - y * wl;
+        const float* src = fmap + ((int64_t)N + (int64_t)(y * win + dy) * g.w[0] + x * win) * fm_rs + c4 * 4;
         // window mean; equals the successive 2x2 means of corr.py:26 up to fp32 rounding
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int dy = 0; dy < win; ++dy)
-          for (int dx = 0; dx < win; ++dx) {
-            const float4 t = __ldg(reinterpret_cast<const float4*>(src + ((int64_t)dy * g.w[0] + dx) * fm_rs));
-            acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
-          }
+        float4 t[8];
+#pragma unroll
+        for (int dx = 0; dx < 8; ++dx)
+          t[dx] = dx < win ? __ldg(reinterpret_cast<const float4*>(src + (int64_t)dx * fm_rs)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 acc = t[0];
+#pragma unroll
+        for (int dx = 1; dx < 8; ++dx) { acc.x += t[dx].x; acc.y += t[dx].y; acc.z += t[dx].z; acc.w += t[dx].w; }
+        for (int o = 1; o < win; o <<= 1) {    // fold the window rows (lanes dy ^ o)
+          acc.x += __shfl_xor_sync(0xffffffffu, acc.x, o); acc.y += __shfl_xor_sync(0xffffffffu, acc.y, o);
+          acc.z += __shfl_xor_sync(0xffffffffu, acc.z, o); acc.w += __shfl_xor_sync(0xffffffffu, acc.w, o);
+        }
         const float inv = 1.f / (float)(win * win);
         v = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
       }
       dh = Phi + (int64_t)r * 256 + c4 * 4;
       dl = Plo + (int64_t)r * 256 + c4 * 4;
     }
+    if (dy != 0) continue;
     const float f[4] = {v.x, v.y, v.z, v.w};
     __nv_bfloat16 h[4], lo[4];
 #pragma unroll
@@ -312,6 +333,11 @@ CgPlan cg_plan(int h0, int w0) {
   p.pk.Ptot = row;
   p.pk.Npad = zt::ceil_div(h0 * w0, 128) * 128;
   p.q_tiles = p.pk.Npad / 128;
+  p.pk.items[0] = (int64_t)p.pk.Npad * 64;
+  for (int i = 0; i < 4; ++i) {
+    const int rows = (i < 3 ? p.pk.row0[i + 1] : p.pk.Ptot) - p.pk.row0[i];
+    p.pk.items[i + 1] = p.pk.items[i] + ((int64_t)rows * 64 << i);
+  }
   return p;
 }
 }  // namespace
@@ -340,7 +366,7 @@ extern "C" int zt_corr_pyramid_f32(const float* fmap, int fm_rs, int h0, int w0,
   __nv_bfloat16* Phi = Qlo + (int64_t)Npad * 256;
   __nv_bfloat16* Plo = Phi + (int64_t)Ptot * 256;
 
-  const int64_t pack_items = (int64_t)(Npad + Ptot) * 64;
+  const int64_t pack_items = p.pk.items[4];
   const int pack_blocks = (int)std::min<int64_t>(ceil_div64(pack_items, 256), 8 * kNumSMs);
   ZT_CUDA(launch_pdl(corr_pack_kernel, dim3(pack_blocks), dim3(256), 0, st, fmap, fm_rs, p.pk, Qhi, Qlo, Phi, Plo));
   if (int rc = check_launch("corr_pack_kernel")) return rc;
