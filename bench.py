@@ -204,56 +204,82 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     _lib.lib()
-    model, sd = build_model(dev)
+    # S frame-range shards of the clip per GPU (each: own model replica, recurrent state and stream; round-robin
+    # enqueue from this thread) - the unit shard.plan deals to GPUs, applied inside one GPU as well (pipeline.py)
+    S = max(1, int(os.environ.get("ZT_SHARDS_PER_GPU", "2")))
+    models = []
+    for _ in range(S):
+        m, sd = build_model(dev)
+        models.append(m)
+    model = models[0]
+    streams = [torch.cuda.Stream(dev) for _ in range(S)]
     K, Wm = args.steps, args.warmup
-    n_frames = min(64, K + Wm + 1)
-    # each rank owns its own shard of the clip (different seed = different frames), halo = frame 0
-    clip_host = synth.synthetic_clip(n_frames, H, W, seed=rank).pin_memory()
-    clip = clip_host.to(dev)
+    n_frames = min(64, (K + S - 1) // S + Wm + 1)
+    # each shard of each rank has its own frames (different seed), halo = frame 0
+    clips_host = [synth.synthetic_clip(n_frames, H, W, seed=rank * S + s).pin_memory() for s in range(S)]
+    clips = [c.to(dev) for c in clips_host]
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def frame(i):
-        return 1 + (i % (n_frames - 1))
+    def frame(j):
+        return 1 + (j % (n_frames - 1))
 
-    def step_dev(i):
-        model.is_new_seq = False
-        return model(clip[frame(i):frame(i) + 1])
+    def step_dev(i, shards=S):
+        s, j = i % shards, i // shards
+        with torch.cuda.stream(streams[s]):
+            models[s].is_new_seq = False
+            return models[s](clips[s][frame(j):frame(j) + 1])
+
+    def timed_dev(shards):
+        """K steady-state frames, round-robin over `shards` shards; device time from the fork to the join."""
+        cur = torch.cuda.current_stream(dev)
+        barrier()
+        l0 = _lib.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(local) as cs:
+            e0.record(cur)
+            for s in range(shards):
+                streams[s].wait_event(e0)
+            for i in range(K):
+                step_dev(Wm * shards + i, shards)
+            for s in range(shards):
+                ev = torch.cuda.Event()
+                ev.record(streams[s])
+                cur.wait_event(ev)
+            e1.record(cur)
+            barrier()
+        return e0.elapsed_time(e1), _lib.launch_count() - l0, cs.summary()
 
     # ---- device-resident throughput ----
-    model.is_new_seq = True
-    model(clip[0:1])                      # halo / new-sequence frame, untimed
-    for i in range(Wm):
+    for s in range(S):
+        with torch.cuda.stream(streams[s]):
+            models[s].is_new_seq = True
+            models[s](clips[s][0:1])      # halo / new-sequence frame, untimed
+    for i in range(Wm * S):
         step_dev(i)
-    barrier()
-    l0 = _lib.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as cs:
-        e0.record()
-        for i in range(K):
-            step_dev(Wm + i)
-        e1.record()
-        barrier()
-    launches = _lib.launch_count() - l0
-    ms = e0.elapsed_time(e1)
-    clocks = cs.summary()
+    single_ms = None
+    if S > 1:
+        single_ms, _, _ = timed_dev(1)    # one shard alone (the per-frame latency path), reported beside the headline
+    ms, launches, clocks = timed_dev(S)
 
-    # ---- end to end through the public host-buffer API (FramePipeline: pinned host frames in, pinned host
-    # H2/H3 out, every frame's H2D and D2H inside the timed region, overlapped with compute on side streams) ----
-    from zero_tig_b200.pipeline import FramePipeline
-    pipe = FramePipeline(model, H, W, depth=int(os.environ.get("ZT_PIPE_DEPTH", "2")))
-    host_frames = [clip_host[frame(i):frame(i) + 1] for i in range(K)]
+    # ---- end to end through the public host-buffer API (MultiShardPipeline / FramePipeline: pinned host frames in,
+    # pinned host H2/H3 out, every frame's H2D and D2H inside the timed region, overlapped with compute on side
+    # streams) ----
+    from zero_tig_b200.pipeline import MultiShardPipeline
+    pipe = MultiShardPipeline(models, H, W, depth=int(os.environ.get("ZT_PIPE_DEPTH", "2")))
+    counts = [K // S + (1 if s < K % S else 0) for s in range(S)]
+    host_frames = [[clips_host[s][frame(j):frame(j) + 1] for j in range(counts[s])] for s in range(S)]
     sink = []
-    pipe.run(host_frames[:min(Wm, 3)], lambda i, a, b: None, new_sequence=False)
+    pipe.run([hf[:min(Wm, 3)] for hf in host_frames], lambda s, i, a, b: None, new_sequence=False)
     barrier()
     t0 = time.perf_counter()
-    pipe.run(host_frames, lambda i, a, b: sink.append(i), new_sequence=False)
+    pipe.run(host_frames, lambda s, i, a, b: sink.append((s, i)), new_sequence=False)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
-    assert sink == list(range(K))
+    assert sorted(sink) == [(s, i) for s in range(S) for i in range(counts[s])]
     barrier()
 
     t = torch.tensor([ms, e2e_s * 1e3], device=dev, dtype=torch.float64)
@@ -278,9 +304,12 @@ def run_b200(args):
         with OpTimer(ops, ["conv2d", "conv2d_bf16", "warp_pair", "corr_lookup", "corr_pyramid", "avgpool2", "instnorm"]) as ot:
             nprof = min(K, 5)
             for i in range(nprof):
-                step_dev(i)
+                step_dev(i, 1)
+            torch.cuda.synchronize()
         eng.USE_GRAPH = use_graph
         tot = ot.totals_ms()
+        # shares are relative to ONE frame chain's step time (kernel times of a lone chain / its ms per frame)
+        step1_ms = (single_ms if single_ms is not None else ms) / K
         frame_ms = tot["conv_frame"][0] / nprof
         raft_ms = tot["conv_raft"][0] / nprof
         warp_ms = tot["warp_pair"][0] / nprof
@@ -298,13 +327,13 @@ def run_b200(args):
                 "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
                 "traffic": TRAFFIC_PER_LAUNCH, "algorithmic_bytes_per_launch": fb / nl,
                 "peak_source": pk["src"] + " copy bandwidth", "ms_per_frame": frame_ms,
-                "avg_launch_ms": frame_ms / nl, "share_of_step": frame_ms / (ms / K),
+                "avg_launch_ms": frame_ms / nl, "share_of_step": frame_ms / step1_ms,
                 "tensor_tflops": ot.flops["conv_frame"] / nprof / frame_ms / 1e9}
         raft_tf = ot.flops["conv_raft"] / nprof / raft_ms / 1e9
         tensor = {"kernel": "conv_tc_kernel + conv_f32_kernel, RAFT launches (M = 3600 positions; bf16 hi/lo split = 3 "
                             "MMAs per useful product)", "bound": "tensor", "achieved": raft_tf, "peak": pk["tf_sust"],
                   "unit": "TFLOP/s (useful fp32-grade)", "frac": raft_tf / pk["tf_sust"], "ms_per_frame": raft_ms,
-                  "share_of_step": raft_ms / (ms / K)}
+                  "share_of_step": raft_ms / step1_ms}
         hbm = []
         for name, byt, t_ms in (("warp_pair", WARP_BYTES, warp_ms), ("corr_lookup", LOOKUP_BYTES_PER_ITER, look_ms),
                                 ("corr_volume+pyramid", 68.4e6 + 7.4e6, corr_ms)):
@@ -316,14 +345,19 @@ def run_b200(args):
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16 tensor-core products, f32 accumulate (Retinex nets: bf16 activations; RAFT: bf16 hi/lo split, f32 storage)", "data": "synthetic",
             "config": {"workload": "RLV inference 1920x1080 (configs[1]), of_scale 3, 12 RAFT iters, steady state, "
-                                   "synthetic %d-frame clip per rank" % n_frames,
+                                   "%d frame-range shard(s) per GPU interleaved on %d stream(s) (one halo frame each, "
+                                   "untimed), synthetic %d-frame clip per shard" % (S, S, n_frames),
                        "l2": "per-frame working set (>2 GB of activations) exceeds the 126 MB L2; no explicit flush",
                        "sharding": "frame ranges + 1 halo frame per rank, no data-path collective"},
             "clocks": clocks,
             "e2e": {"value": world * K / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": pipe.h2d_bytes,
                     "d2h_bytes_per_step": pipe.d2h_bytes,
-                    "api": "zero_tig_b200.pipeline.FramePipeline.run (pinned host fp32 frames in, pinned host fp32 "
-                           "H2/H3 out; copies on side streams)"},
+                    "api": "zero_tig_b200.pipeline.MultiShardPipeline.run (one FramePipeline per shard: pinned host fp32 "
+                           "frames in, pinned host fp32 H2/H3 out; copies on side streams)"},
+            "shards_per_gpu": S,
+            "single_shard": None if single_ms is None else {
+                "value": world * K / (single_ms / 1e3), "unit": UNIT, "ms_per_step": single_ms / K,
+                "note": "one shard alone on the GPU (per-frame latency path), same K frames, device-timed"},
             "gpu_launches": int(launches), "roofline": roof, "tensor_kernels": [tensor], "hbm_kernels": hbm,
         }
         if train is not None:

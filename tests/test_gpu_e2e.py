@@ -174,3 +174,27 @@ def test_full_size_clip_vs_oracle(H, W, dataset, n, weights, tmp_path):
     fu = [v for k, v in m.raft.engine().ws.bufs.items() if k[0] == "flow_up"][0]
     assert fu.shape == tr["flow_up"].shape
     assert epe(fu.cpu(), tr["flow_up"]) <= EPE_TOL
+
+
+def test_multi_shard_pipeline_equals_per_shard_runs(model_factory):
+    """Two frame-range shards interleaved on two streams of one GPU (MultiShardPipeline) return, per shard and in
+    order, bit-identical frames to a lone FramePipeline over the same (halo + range) sub-clip."""
+    from zero_tig_b200 import synth
+    from zero_tig_b200.pipeline import FramePipeline, MultiShardPipeline
+    H, W = 128, 160
+    clip = synth.synthetic_clip(11, H, W, seed=13)
+    # shard 0: frames 0..5; shard 1: halo frame 5 + frames 6..10 (shard.plan's cut)
+    subs = [[clip[t:t + 1].pin_memory() for t in range(0, 6)], [clip[t:t + 1].pin_memory() for t in range(5, 11)]]
+    want = []
+    for frames in subs:
+        got = []
+        FramePipeline(model_factory(1), H, W).run(frames, lambda i, a, b: got.append((i, a.clone(), b.clone())))
+        want.append(got)
+    multi = [[], []]
+    mp = MultiShardPipeline([model_factory(1), model_factory(1)], H, W)
+    mp.run(subs, lambda s, i, a, b: multi[s].append((i, a.clone(), b.clone())))
+    torch.cuda.synchronize()
+    for s in range(2):
+        assert [i for i, _, _ in multi[s]] == list(range(6))
+        for (i, a, b), (j, ra, rb) in zip(multi[s], want[s]):
+            assert i == j and torch.equal(a, ra) and torch.equal(b, rb), (s, i)

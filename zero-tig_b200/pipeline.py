@@ -37,6 +37,12 @@ class FramePipeline:
         """frames: sequence of pinned host tensors [1,3,H,W] fp32 (one sequence, in order).
         emit(i, H2_host, H3_host) is called in order once frame i's outputs are in host memory; the host
         buffers are reused ``depth`` frames later."""
+        for _ in self.steps(frames, emit, new_sequence):
+            pass
+
+    def steps(self, frames, emit, new_sequence=True):
+        """Generator form of ``run``: enqueues one frame per ``next()`` on the stream that is current at that
+        moment (callers that interleave several pipelines keep one stream per pipeline, see ``MultiShardPipeline``)."""
         from . import ops
         n = len(frames)
         if n == 0:
@@ -68,7 +74,53 @@ class FramePipeline:
                 self.host_out[slot][1].copy_(H3, non_blocking=True)
                 self.ev_out[slot].record(self.d2h)
             keep[slot] = (H2, H3)                    # keep the device tensors alive until their D2H completes
+            yield i
         for i in range(max(0, n - self.depth), n):
             slot = i % self.depth
             self.ev_out[slot].synchronize()
             emit(i, *self.host_out[slot])
+
+
+class MultiShardPipeline:
+    """Several frame-range shards of a clip on ONE GPU (the same unit ``shard.plan`` deals to the GPUs of a box: a
+    contiguous frame range preceded by one halo frame), each with its own model replica, recurrent state,
+    ``FramePipeline`` and compute stream; frames are enqueued round-robin from one host thread.
+
+    Why: a frame is ~250 dependent launches, most of them RAFT update-block kernels on a 45x80 grid that occupy
+    <= 120 of the 148 SMs and spend half their time in prologue / pipeline fill / drain.  A second, independent
+    frame chain on another stream fills those holes (1080p: 200 -> 220 frames/s with two shards).  Every shard
+    computes exactly what a single ``FramePipeline`` over its (halo + range) sub-clip computes.
+    """
+
+    def __init__(self, models, H, W, depth=2, quantize_u8=False):
+        if not models:
+            raise ValueError("MultiShardPipeline needs at least one model replica")
+        self.pipes = [FramePipeline(m, H, W, depth=depth, quantize_u8=quantize_u8) for m in models]
+        self.dev = self.pipes[0].dev
+        self.streams = [torch.cuda.Stream(self.dev) for _ in models]
+        self.h2d_bytes, self.d2h_bytes = self.pipes[0].h2d_bytes, self.pipes[0].d2h_bytes
+
+    def run(self, shard_frames, emit, new_sequence=True):
+        """shard_frames[s]: the pinned host frames of shard s, in order (its halo frame first when ``new_sequence``).
+        emit(s, i, H2_host, H3_host) is called in frame order within each shard."""
+        if len(shard_frames) != len(self.pipes):
+            raise ValueError("expected %d frame lists, got %d" % (len(self.pipes), len(shard_frames)))
+        cur = torch.cuda.current_stream(self.dev)
+        start = torch.cuda.Event()
+        start.record(cur)
+        gens = []
+        for s, (pipe, frames) in enumerate(zip(self.pipes, shard_frames)):
+            self.streams[s].wait_event(start)
+            gens.append(pipe.steps(frames, (lambda i, a, b, _s=s: emit(_s, i, a, b)), new_sequence))
+        live = list(range(len(gens)))
+        while live:
+            for s in list(live):
+                with torch.cuda.stream(self.streams[s]):
+                    try:
+                        next(gens[s])
+                    except StopIteration:
+                        live.remove(s)
+        for st in self.streams:                       # the caller's stream continues after every shard
+            done = torch.cuda.Event()
+            done.record(st)
+            cur.wait_event(done)
