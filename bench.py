@@ -421,15 +421,21 @@ def cpu_baseline(sd):
     from zero_tig_b200 import synth
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    clip = synth.synthetic_clip(2, H, W, seed=0)
+    n = int(os.environ.get("ZT_CPU_BASELINE_FRAMES", "8"))      # ~1.5 s per 1080p frame on 16 cores -> ~12 s of CPU work
+    clip = synth.synthetic_clip(n + 1, H, W, seed=0)
     st = O.InferState()
     sdc = {k: v.cpu() for k, v in sd.items()}
     O.finetune_forward(clip[0:1], sdc, st, True, OF_SCALE)
     t0 = time.time()
-    O.finetune_forward(clip[1:2], sdc, st, False, OF_SCALE)
+    done = 0
+    for t in range(1, n + 1):
+        O.finetune_forward(clip[t:t + 1], sdc, st, False, OF_SCALE)
+        done += 1
+        if time.time() - t0 > 30.0:
+            break
     dt = time.time() - t0
-    return {"value": 1.0 / dt, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": "1 steady-state 1080p frame after 1 new-sequence frame (%.1f s)" % dt}
+    return {"value": done / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "%d steady-state 1080p frames after 1 new-sequence frame (%.1f s of CPU work)" % (done, dt)}
 
 
 def main():

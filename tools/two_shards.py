@@ -1,4 +1,4 @@
-"""GPU experiment: S independent frame-range shards of a 1080p clip on ONE GPU, one model instance + one stream per
+"""GPU tool (python tools/two_shards.py S K [H W]): S independent frame-range shards of a 1080p clip on ONE GPU, one model instance + one stream per
 shard, frames enqueued round-robin from one host thread.  Prints frames/s against the single-shard loop."""
 import os
 import sys
@@ -13,13 +13,14 @@ from zero_tig_b200 import synth                        # noqa: E402
 
 S = int(sys.argv[1]) if len(sys.argv) > 1 else 2
 K = int(sys.argv[2]) if len(sys.argv) > 2 else 30
-H, W = 1080, 1920
+H, W = (int(sys.argv[3]), int(sys.argv[4])) if len(sys.argv) > 4 else (1080, 1920)
+NF = 12 if H <= 1080 else 6
 dev = torch.device("cuda")
 models, clips, streams = [], [], []
 for s in range(S):
     m, _ = bench.build_model(dev)
     models.append(m)
-    clips.append(synth.synthetic_clip(12, H, W, seed=s).to(dev))
+    clips.append(synth.synthetic_clip(NF, H, W, seed=s, underwater=(H > 1080)).to(dev))
     streams.append(torch.cuda.Stream())
 torch.cuda.synchronize()
 
@@ -29,7 +30,7 @@ def run(n, shards):
         for s in shards:
             with torch.cuda.stream(streams[s]):
                 models[s].is_new_seq = False
-                models[s](clips[s][1 + i % 11:2 + i % 11])
+                models[s](clips[s][1 + i % (NF - 1):2 + i % (NF - 1)])
 
 
 for s in range(S):
@@ -44,4 +45,4 @@ for shards in ([0], list(range(S))):
     run(K, shards)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
-    print("shards on the GPU: %d  %.1f frames/s (%.2f ms per frame)" % (len(shards), K * len(shards) / dt, 1e3 * dt / (K * len(shards))))
+    print("%dx%d shards on the GPU: %d  %.1f frames/s (%.2f ms per frame)" % (W, H, len(shards), K * len(shards) / dt, 1e3 * dt / (K * len(shards))))
