@@ -206,7 +206,7 @@ def run_b200(args):
     _lib.lib()
     # S frame-range shards of the clip per GPU (each: own model replica, recurrent state and stream; round-robin
     # enqueue from this thread) - the unit shard.plan deals to GPUs, applied inside one GPU as well (pipeline.py)
-    S = max(1, int(os.environ.get("ZT_SHARDS_PER_GPU", "2")))
+    S = max(1, int(os.environ.get("ZT_SHARDS_PER_GPU", "3")))
     models = []
     for _ in range(S):
         m, sd = build_model(dev)
