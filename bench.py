@@ -339,7 +339,10 @@ def run_b200(args):
                                 ("corr_volume+pyramid", 68.4e6 + 7.4e6, corr_ms)):
             gbs = byt / t_ms / 1e6
             hbm.append({"kernel": name, "bound": "hbm", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s",
-                        "frac": gbs / pk["hbm"], "ms": t_ms})
+                        "frac": gbs / pk["hbm"], "ms": t_ms,
+                        "timing": "CUDA events around each call in the eager (un-graphed) frame loop, cold caches; "
+                                  "includes ~10 us of launch/event overhead per call (ncu kernel times: "
+                                  "profiles/r01_launches_200fps.txt, r01_ncu_hbm_kernels.txt)"})
         out = {
             "metric": METRIC, "value": world * K / (ms / 1e3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
