@@ -323,19 +323,27 @@ __global__ void __launch_bounds__(256) pack_nhwc_bf16_kernel(const float* __rest
 // fast path: three channels per source, four consecutive pixels per thread (float4 plane loads, 4*CS*2 contiguous
 // bytes written per thread), channel placement resolved at compile time
 template <int CS, int NSRC>
-__global__ void __launch_bounds__(256) pack_nhwc_bf16_x4_kernel(const float* __restrict__ s0, const float* __restrict__ s1,
+__global__ void __launch_bounds__(256, 4) pack_nhwc_bf16_x4_kernel(const float* __restrict__ s0, const float* __restrict__ s1,
                                                                 const float* __restrict__ s2, const float* __restrict__ s3,
                                                                 float add, __nv_bfloat16* __restrict__ out, int64_t HW) {
+  __shared__ uint4 stage[8][32 * (4 * CS / 8)];
   pdl_enter();
   const float* src[4] = {s0, s1, s2, s3};
   const int64_t n4 = HW >> 2;
+  // n4 is a multiple of 32 (checked by the host): whole warps iterate together (shared-memory transpose below)
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
     float4 v[NSRC * 3];
 #pragma unroll
     for (int s = 0; s < NSRC; ++s)
 #pragma unroll
-      for (int c = 0; c < 3; ++c) v[s * 3 + c] = __ldg(reinterpret_cast<const float4*>(src[s] + c * HW) + i);
-    uint4* o = reinterpret_cast<uint4*>(out + i * 4 * CS);
+      for (int c = 0; c < 3; ++c)
+        v[s * 3 + c] = __ldg(reinterpret_cast<const float4*>(src[s] + c * HW) + i);
+    // Each thread owns 4*CS*2 contiguous output bytes; stored directly a warp store would touch 32 lines with 16 B
+    // each.  The warp's 32 * U uint4 go through shared memory (XOR-swizzled against bank conflicts) so that every
+    // store instruction writes 512 contiguous bytes.
+    constexpr int U = 4 * CS / 8;                       // uint4 per thread (4 or 8)
+    uint4* tile = stage[threadIdx.x >> 5];
+    const int lane = threadIdx.x & 31;
 #pragma unroll
     for (int px = 0; px < 4; ++px) {
       float r[CS];
@@ -349,10 +357,22 @@ __global__ void __launch_bounds__(256) pack_nhwc_bf16_x4_kernel(const float* __r
         }
       }
 #pragma unroll
-      for (int j = 0; j < CS / 8; ++j)
-        o[px * (CS / 8) + j] = make_uint4(pack_bf16x2(r[8 * j], r[8 * j + 1]), pack_bf16x2(r[8 * j + 2], r[8 * j + 3]),
-                                          pack_bf16x2(r[8 * j + 4], r[8 * j + 5]), pack_bf16x2(r[8 * j + 6], r[8 * j + 7]));
+      for (int j = 0; j < CS / 8; ++j) {
+        const int u = px * (CS / 8) + j;
+        tile[lane * U + (u ^ (lane & (U - 1)))] =
+            make_uint4(pack_bf16x2(r[8 * j], r[8 * j + 1]), pack_bf16x2(r[8 * j + 2], r[8 * j + 3]),
+                       pack_bf16x2(r[8 * j + 4], r[8 * j + 5]), pack_bf16x2(r[8 * j + 6], r[8 * j + 7]));
+      }
     }
+    __syncwarp();
+    uint4* o = reinterpret_cast<uint4*>(out) + (i - lane) * U;   // the warp's 32 * U contiguous uint4
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      const int e = k * 32 + lane;                      // element e belongs to lane e / U of this iteration
+      const int t = e / U, u = e % U;
+      o[e] = tile[t * U + (u ^ (t & (U - 1)))];
+    }
+    __syncwarp();
   }
 }
 
@@ -408,8 +428,8 @@ extern "C" int zt_pack_nhwc_bf16(const float* s0, const float* s1, const float* 
   ZT_REQUIRE((nsrc < 2 || s1) && (nsrc < 3 || s2) && (nsrc < 4 || s3), "pack_nhwc_bf16: missing source");
   ZT_REQUIRE(cs == 8 || cs == 16, "pack_nhwc_bf16: cs must be 8 or 16 (got %d)", cs);
   const bool al16 = (((uintptr_t)s0 | (uintptr_t)s1 | (uintptr_t)s2 | (uintptr_t)s3) & 15) == 0;
-  if (c_each == 3 && (HW & 3) == 0 && al16 && nsrc * 3 <= cs) {
-    const int b4 = (int)std::min<int64_t>(ceil_div64(HW >> 2, 256), 8 * kNumSMs);
+  if (c_each == 3 && (HW & 127) == 0 && al16 && nsrc * 3 <= cs) {
+    const int b4 = (int)std::min<int64_t>(ceil_div64(HW >> 2, 256), 64 * kNumSMs);   // one item per thread up to 4K frames
     cudaStream_t st = (cudaStream_t)stream;
     __nv_bfloat16* o = (__nv_bfloat16*)out;
     cudaError_t e = cudaErrorInvalidValue;
