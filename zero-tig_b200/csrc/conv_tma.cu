@@ -323,7 +323,7 @@ __global__ void __launch_bounds__(256) pack_nhwc_bf16_kernel(const float* __rest
 // fast path: three channels per source, four consecutive pixels per thread (float4 plane loads, 4*CS*2 contiguous
 // bytes written per thread), channel placement resolved at compile time
 template <int CS, int NSRC>
-__global__ void __launch_bounds__(256, 4) pack_nhwc_bf16_x4_kernel(const float* __restrict__ s0, const float* __restrict__ s1,
+__global__ void __launch_bounds__(256, 3) pack_nhwc_bf16_x4_kernel(const float* __restrict__ s0, const float* __restrict__ s1,
                                                                 const float* __restrict__ s2, const float* __restrict__ s3,
                                                                 float add, __nv_bfloat16* __restrict__ out, int64_t HW) {
   __shared__ uint4 stage[8][32 * (4 * CS / 8)];
