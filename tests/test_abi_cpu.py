@@ -65,3 +65,20 @@ def test_no_cpu_fallback(weights, tmp_path):
     m = Finetunemodel(synth.make_args(model_pretrain=str(ck)))
     with pytest.raises(RuntimeError, match="CUDA"):
         m(torch.rand(1, 3, 64, 64))
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the loud failure on a box without a GPU")
+def test_pipelines_refuse_to_run_without_gpu(weights, tmp_path):
+    """FramePipeline / MultiShardPipeline only move pinned buffers around the CUDA path: no device, no pipeline."""
+    from zero_tig_b200 import synth
+    from zero_tig_b200.model.model import Finetunemodel
+    from zero_tig_b200.pipeline import FramePipeline, MultiShardPipeline
+    ck = tmp_path / "w.pt"
+    torch.save(weights, ck)
+    m = Finetunemodel(synth.make_args(model_pretrain=str(ck)))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        FramePipeline(m, 64, 64)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        MultiShardPipeline([m, m], 64, 64)
+    with pytest.raises(ValueError):
+        MultiShardPipeline([], 64, 64)
