@@ -61,6 +61,10 @@ class RaftEngine:
     # 90 / 60 CTAs on the K loop and change the iteration time by < 1 %: these launches are not K-loop bound)
     BN_C2 = int(os.environ.get("ZT_BN_C2", "64"))
     BN_ENC = int(os.environ.get("ZT_BN_ENC", "64"))
+    BN_ZR = int(os.environ.get("ZT_BN_ZR", "128"))      # GRU z|r conv (N = 256)
+    BN_Q = int(os.environ.get("ZT_BN_Q", "64"))        # GRU q conv (N = 128)
+    BN_C1 = int(os.environ.get("ZT_BN_C1", "128"))      # motion encoder convc1 (N = 256)
+    BN_FH = int(os.environ.get("ZT_BN_FH", "128"))      # flow head conv1 (N = 256)
 
     def __init__(self, raft):
         self.raft = raft
@@ -338,7 +342,7 @@ class RaftEngine:
                 ops.conv2d(w["enc.convf2"], f1, 128, 128, 1, h8, w8, c2f, 256, out_off=192, pad=(1, 1), act="relu", tc=T,
                            bn=32)
             ops.corr_lookup(lv, hs, wsz, coords1, corr, 324, N)   # correlation branch (update.py:90-91)
-            ops.conv2d(w["enc.convc1"], corr, 324, 324, 1, h8, w8, c1, 256, act="relu", tc=T, bn=64)
+            ops.conv2d(w["enc.convc1"], corr, 324, 324, 1, h8, w8, c1, 256, act="relu", tc=T, bn=self.BN_C1)
             ops.conv2d(w["enc.convc2"], c1, 256, 256, 1, h8, w8, c2f, 256, pad=(1, 1), act="relu", tc=T, bn=self.BN_C2)
             join()
             ops.conv2d(w["enc.conv"], c2f, 256, 256, 1, h8, w8, hx, 384, out_off=256, pad=(1, 1), act="relu", tc=T,
@@ -347,16 +351,16 @@ class RaftEngine:
                 if T:
                     ops.conv2d(w[f"gru.zr{s}.hm"], hx, 384, 128, 1, h8, w8, rh, 128, in1=hx, in1_cs=384, c1=128,
                                in1_off=256, pad=pad, epi="gru_zr", aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128, tc=T,
-                               bn=64, bplane=gru_pre["zr" + s], bplane_cs=256)
+                               bn=self.BN_ZR, bplane=gru_pre["zr" + s], bplane_cs=256)
                     ops.conv2d(w[f"gru.q{s}.hm"], rh, 128, 128, 1, h8, w8, hx, 384, in1=hx, in1_cs=384, c1=128,
                                in1_off=256, pad=pad, epi="gru_q", aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128, tc=T,
-                               bn=32, bplane=gru_pre["q" + s], bplane_cs=128)
+                               bn=self.BN_Q, bplane=gru_pre["q" + s], bplane_cs=128)
                     continue
                 ops.conv2d(w["gru.zr" + s], hx, 384, 384, 1, h8, w8, rh, 128, pad=pad, epi="gru_zr",
                            aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128, tc=T, bn=64)
                 ops.conv2d(w["gru.q" + s], rh, 128, 128, 1, h8, w8, hx, 384, in1=hx, in1_cs=384, c1=256,
                            in1_off=128, pad=pad, epi="gru_q", aux0=hx, aux0_cs=384, aux1=z, aux1_cs=128, tc=T, bn=32)
-            ops.conv2d(w["fh1"], hx, 384, 128, 1, h8, w8, fhid, 256, pad=(1, 1), act="relu", tc=TH, bn=64)
+            ops.conv2d(w["fh1"], hx, 384, 128, 1, h8, w8, fhid, 256, pad=(1, 1), act="relu", tc=TH, bn=self.BN_FH)
             if TH:     # flow head conv2 + coords1 += delta + flow outputs in one launch
                 ops.flow_head2_update(fhid, 256, 256, w["fh2.raw"][0], w["fh2.raw"][1], coords1, flow4, 4, hx, 384, 382,
                                       h8, w8)
