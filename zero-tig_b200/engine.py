@@ -59,7 +59,7 @@ class RaftEngine:
     BN96 = int(os.environ.get("ZT_ENC_BN96", "1"))
     # N tiles of the two K = 2304 layers of the motion encoder (measured: 48 / 32 instead of 64 put 120 instead of
     # 90 / 60 CTAs on the K loop and change the iteration time by < 1 %: these launches are not K-loop bound)
-    BN_C2 = int(os.environ.get("ZT_BN_C2", "64"))
+    BN_C2 = int(os.environ.get("ZT_BN_C2", "96"))
     BN_ENC = int(os.environ.get("ZT_BN_ENC", "64"))
     BN_ZR = int(os.environ.get("ZT_BN_ZR", "128"))      # GRU z|r conv (N = 256)
     BN_Q = int(os.environ.get("ZT_BN_Q", "64"))        # GRU q conv (N = 128)
