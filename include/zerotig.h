@@ -10,7 +10,7 @@
  * The reference (L-Forster/Zero-TIG) has no native code and therefore no FFI of its
  * own: each entry point below names the reference Python function
  * (file:line under the upstream tree) whose torch ops it replaces.  The host-side
- * binding is ctypes (zero-tig_b200/_lib.py); INTEGRATION.md shows the stub.
+ * binding is ctypes (zero_tig_b200/_lib.py); INTEGRATION.md shows the stub.
  *
  * Internal activation layout: NHWC fp32 ("pixel-major", channel stride `cs` >= C,
  * cs % 4 == 0, base pointers 16-byte aligned).  Frame-level tensors that cross the

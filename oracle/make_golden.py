@@ -54,7 +54,7 @@ def main():
     sd = synth.synthetic_state_dict(net.state_dict(), seed=1234)
 
     # ---- Finetunemodel clips ----
-    def run_clip(tag, H, W, of_scale, n_frames, stride):
+    def run_clip(tag, H, W, of_scale, n_frames, stride, keep=None):
         a = synth.make_args(of_scale=of_scale)
         with tempfile.NamedTemporaryFile(suffix=".pt") as tf:
             torch.save({k: v for k, v in sd.items() if not k.startswith("raft.")}, tf.name)
@@ -76,6 +76,8 @@ def main():
             for t in range(n_frames):
                 m.is_new_seq = (t == 0)
                 H2, H3, s3 = m(clip[t:t + 1])
+                if keep is not None and t not in keep:
+                    continue
                 out[f"H2_{t}"] = H2[0, :, ::stride, ::stride].numpy().copy()
                 out[f"H3_{t}"] = H3[0, :, ::stride, ::stride].numpy().copy()
                 out[f"s3_{t}"] = s3[0, :, ::stride, ::stride].numpy().copy()
@@ -90,6 +92,8 @@ def main():
 
     run_clip("s1_128x160", 128, 160, 1, 3, 1)
     run_clip("s3_390x400", 390, 400, 3, 3, 3)
+    # BASELINE.md gate "per frame, through frame 63": the recurrence of model.py:324-339 over a 64-frame clip
+    run_clip("s3_390x400_64", 390, 400, 3, 64, 3, keep=(0, 1, 7, 15, 31, 47, 62, 63))
 
     # ---- per-op vectors ----
     g = torch.Generator().manual_seed(11)

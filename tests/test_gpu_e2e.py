@@ -33,7 +33,7 @@ def model_factory(weights, tmp_path_factory):
 def test_finetune_clip_vs_reference_golden(tag, model_factory):
     from zero_tig_b200 import synth, _lib
     g = np.load(os.path.join(GOLDEN, f"infer_{tag}.npz"))
-    H, W, of_scale, n, stride = [int(v) for v in g["meta"]]
+    H, W, of_scale, n, stride = [int(v) for v in g["meta"][:5]]
     clip = synth.synthetic_clip(n, H, W, seed=3).cuda()
     m = model_factory(of_scale)
     before = _lib.launch_count()

@@ -15,18 +15,26 @@ NAMES = ("L_pred1 L_pred2 L2 s2 s21 s22 H2 H11 H12 H13 s13 H14 s14 H3 s3 H3_pred
          "L_pred1_L_pred2_diff H3_denoised1_H3_denoised2_diff H2_blur H3_blur H3_denoised1 H3_denoised2").split()
 
 
-@pytest.mark.parametrize("tag", ["rlv", "uw"])
+def _meta(g):
+    m = [int(v) for v in g["meta"]]
+    return m[:5] + [m[5] if len(m) > 5 else 3]
+
+
+# "540x960" = BASELINE.json configs[2] at its real size, of_scale 3: RAFT input 180 rows padded to 184 (Q3), swapped
+# warp scales 540/184 vs 960/320 (Q2) - fixture from the unmodified reference (oracle/make_golden_train.py)
+@pytest.mark.parametrize("tag", ["rlv", "uw", "540x960"])
 def test_network_forward_loss_vs_reference_golden(tag, weights):
     import zt_oracle as O
     from zero_tig_b200 import synth
     from zero_tig_b200.model.model import Network
     g = np.load(os.path.join(GOLDEN, f"train_{tag}.npz"))
-    H, W, of_scale, n, stride = [int(v) for v in g["meta"]]
+    H, W, of_scale, n, stride, seed = _meta(g)
+    torch.set_num_threads(os.cpu_count() or 1)
     net = Network(synth.make_args(dataset="underwater" if tag == "uw" else "RLV", of_scale=of_scale)).cuda()
     net.load_state_dict(weights)
     net.train()
     assert net.is_WB == (tag == "uw")
-    clip = synth.synthetic_clip(n, H, W, seed=3, underwater=(tag == "uw"))
+    clip = synth.synthetic_clip(n, H, W, seed=seed, underwater=(tag == "uw"))
     st = O.TrainState()
     for t in range(n):
         x = clip[t:t + 1].cuda()
@@ -59,6 +67,9 @@ def test_network_forward_loss_vs_reference_golden(tag, weights):
         st.last_H3, st.last_s3 = o_outs[13], o_outs[14]
         got_terms = net.last_loss_terms.cpu()
         for name, a, b in zip(O.LOSS_NAMES, got_terms.tolist(), [float(v) for v in o_terms]):
+            assert abs(a - b) <= 1e-3 * abs(b) + 1e-6, (name, t, a, b)
+        # ... and against the 17 weighted terms the UNMODIFIED reference produced (loss.py:46-77, call order)
+        for name, a, b in zip(O.LOSS_NAMES, got_terms.tolist(), g[f"terms_{t}"].tolist()):
             assert abs(a - b) <= 1e-3 * abs(b) + 1e-6, (name, t, a, b)
         net.load_state_dict(weights)
 
@@ -116,7 +127,7 @@ _TRUNK = ("enhance.in_conv.0.weight", "enhance.in_conv.0.bias", "enhance.conv.0.
           "enhance.conv.1.bias")
 
 
-@pytest.mark.parametrize("tag", ["rlv", "uw"])
+@pytest.mark.parametrize("tag", ["rlv", "uw", "540x960"])
 def test_loss_backward_vs_reference_golden(tag, weights):
     """loss.backward() through Network._loss fills .grad of the 20 trainable tensors; compared with the
     gradients of the unmodified reference on frame 1 of the golden clip (RAFT + warp in the loop)."""
@@ -124,11 +135,11 @@ def test_loss_backward_vs_reference_golden(tag, weights):
     from zero_tig_b200.engine import TRAIN_PARAMS
     from zero_tig_b200.model.model import Network
     g = np.load(os.path.join(GOLDEN, f"train_{tag}.npz"))
-    H, W, of_scale, n, stride = [int(v) for v in g["meta"]]
+    H, W, of_scale, n, stride, seed = _meta(g)
     net = Network(synth.make_args(dataset="underwater" if tag == "uw" else "RLV", of_scale=of_scale)).cuda()
     net.load_state_dict(weights)
     net.train()
-    clip = synth.synthetic_clip(n, H, W, seed=3, underwater=(tag == "uw"))
+    clip = synth.synthetic_clip(n, H, W, seed=seed, underwater=(tag == "uw"))
     for t in range(n):
         x = clip[t:t + 1].cuda()
         net.is_new_seq = (t == 0)

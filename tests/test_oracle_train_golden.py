@@ -12,13 +12,16 @@ NAMES = ("L_pred1 L_pred2 L2 s2 s21 s22 H2 H11 H12 H13 s13 H14 s14 H3 s3 H3_pred
          "L_pred1_L_pred2_diff H3_denoised1_H3_denoised2_diff H2_blur H3_blur H3_denoised1 H3_denoised2").split()
 
 
-@pytest.mark.parametrize("tag", ["rlv", "uw"])
+@pytest.mark.parametrize("tag", ["rlv", "uw", "540x960"])
 def test_network_forward_and_loss_vs_reference(tag, weights):
+    """"540x960" is BASELINE.json configs[2] at its real size (of_scale 3: pad 180 -> 184 rows, swapped warp scales)."""
     import zt_oracle as O
     from zero_tig_b200 import synth
     g = np.load(os.path.join(GOLDEN, f"train_{tag}.npz"))
-    H, W, of_scale, n, stride = [int(v) for v in g["meta"]]
-    clip = synth.synthetic_clip(n, H, W, seed=3, underwater=(tag == "uw"))
+    meta = [int(v) for v in g["meta"]]
+    H, W, of_scale, n, stride = meta[:5]
+    torch.set_num_threads(os.cpu_count() or 1)
+    clip = synth.synthetic_clip(n, H, W, seed=meta[5] if len(meta) > 5 else 3, underwater=(tag == "uw"))
     st = O.TrainState()
     for t in range(n):
         x = clip[t:t + 1]
@@ -35,6 +38,9 @@ def test_network_forward_and_loss_vs_reference(tag, weights):
         total = float(sum(terms))
         ref_loss = float(g[f"loss_{t}"])
         assert abs(total - ref_loss) <= 1e-4 * abs(ref_loss), (t, total, ref_loss)
+        # each of the 17 weighted terms against the reference's own (spied) values, loss.py:46-77
+        for name, a, b in zip(O.LOSS_NAMES, [float(v) for v in terms], g[f"terms_{t}"].tolist()):
+            assert abs(a - b) <= 1e-4 * abs(b) + 1e-7, (name, t, a, b)
         st.last_H3, st.last_s3 = outs[13], outs[14]
 
 

@@ -1,6 +1,6 @@
 """GPU debug tool: gradients of Network._loss (CUDA backward) vs the reference goldens and vs autograd
 over the CPU oracle.  Prints the relative L2 error per trainable tensor.
-    python tools/grad_check.py [rlv|uw]
+    python tools/grad_check.py [rlv|uw|540x960]
 """
 import os
 import sys
@@ -19,13 +19,15 @@ from zero_tig_b200.model.model import Network          # noqa: E402
 def main():
     tag = sys.argv[1] if len(sys.argv) > 1 else "rlv"
     g = np.load(os.path.join(ROOT, "tests", "golden", f"train_{tag}.npz"))
-    H, W, of_scale, n, stride = [int(v) for v in g["meta"]]
+    meta = [int(v) for v in g["meta"]]
+    H, W, of_scale, n, stride = meta[:5]
+    seed = meta[5] if len(meta) > 5 else 3
     tmpl = Network(synth.make_args()).state_dict()
     weights = synth.synthetic_state_dict(tmpl, seed=1234)
     net = Network(synth.make_args(dataset="underwater" if tag == "uw" else "RLV", of_scale=of_scale)).cuda()
     net.load_state_dict(weights)
     net.train()
-    clip = synth.synthetic_clip(n, H, W, seed=3, underwater=(tag == "uw"))
+    clip = synth.synthetic_clip(n, H, W, seed=seed, underwater=(tag == "uw"))
     wreq = {k: (v.clone().requires_grad_(True) if k in TRAIN_PARAMS else v) for k, v in weights.items()}
     st = O.TrainState()
     for t in range(n):

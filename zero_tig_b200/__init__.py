@@ -1,10 +1,13 @@
-"""Import shim: the product package lives in the directory ``zero-tig_b200/`` (a
-hyphen is not a legal Python identifier), so ``import zero_tig_b200`` resolves here
-and forwards to that directory."""
-import os as _os
+"""zero-tig-b200: B200-native (sm_100a) implementation of the Zero-TIG per-frame-pair hot
+path (RAFT flow -> backward warp -> illumination-guided enhance/denoise nets) behind the
+reference's ``model/model.py`` interface.  See DESIGN.md / INTEGRATION.md at the repo root.
+"""
+__version__ = "0.1.0"
 
-_real = _os.path.normpath(_os.path.join(_os.path.dirname(_os.path.abspath(__file__)), "..", "zero-tig_b200"))
-__path__ = [_real]
-__file__ = _os.path.join(_real, "__init__.py")
-with open(__file__, "r") as _f:
-    exec(compile(_f.read(), __file__, "exec"))
+from . import _lib  # noqa: F401  (ctypes binding; loading is lazy)
+
+
+def build(force=False, verbose=False):
+    """Compile csrc/*.cu into csrc/libzerotig.so with nvcc for sm_100a."""
+    from .build import build as _b
+    return _b(force=force, verbose=verbose)

@@ -1,7 +1,7 @@
 """In-tree nvcc build of libzerotig.so for sm_100a (no JIT cache, no torch headers).
 
 ``python -m zero_tig_b200.build`` or ``zero_tig_b200.build.build()``.  Objects and the
-shared library land in ``zero-tig_b200/csrc/`` so the built library travels with a
+shared library land in ``zero_tig_b200/csrc/`` so the built library travels with a
 snapshot of the repository.
 """
 import concurrent.futures as cf

@@ -33,8 +33,21 @@ class _Workspace:
         return t
 
 
+# Parameters can be updated through raw pointers (optim.ClipAdam's fused kernel, bn_train's running statistics):
+# torch's per-tensor ``_version`` does not see those writes, so every such writer bumps a generation counter of the
+# tensors it wrote (keyed by device address) and the packed-weight caches key on it as well.
+_PARAM_GENERATION = {}
+
+
+def bump_param_generation(tensors):
+    for t in tensors:
+        k = t.data_ptr()
+        _PARAM_GENERATION[k] = _PARAM_GENERATION.get(k, 0) + 1
+
+
 def _param_version(module):
-    return tuple((p.data_ptr(), p._version) for p in list(module.parameters()) + list(module.buffers()))
+    return tuple((p.data_ptr(), p._version, _PARAM_GENERATION.get(p.data_ptr(), 0))
+                 for p in list(module.parameters()) + list(module.buffers()))
 
 
 # ----------------------------------------------------------------------------------------
@@ -648,6 +661,7 @@ class TrainEngine(FrameEngine):
             ops.bn_train(t[k], 64, cur[k + 1], 64, cur[k], 64, st[k], bn.weight, bn.bias, bn.running_mean,
                          bn.running_var, HW, 64, bn.eps, bn.momentum)
             bn.num_batches_tracked += 1
+        bump_param_generation((bn.running_mean, bn.running_var))   # written through raw pointers
         ops.conv2d(w["e.out"], cur[3], 64, 64, 1, H, W, s4, 4, pad=(1, 1), act="sigmoid", tc=self.TC_ENH)
         s2, H2 = torch.empty_like(x), torch.empty_like(x)
         ops.retinex_h2(x, s4, 4, s2, H2, HW, self.EPS)

@@ -102,6 +102,12 @@ class Finetunemodel(nn.Module, _Recurrent):
         return _make_raft(args)
 
     def forward(self, input):
+        if self.enhance.training:
+            # the reference's Finetunemodel in train() mode would normalise with batch statistics and update the
+            # running ones; the inference engine folds the running statistics into the block convolution
+            # (predict.py:78 always calls eval()).  Refuse instead of silently diverging.
+            raise RuntimeError("Finetunemodel.forward runs eval-mode BatchNorm only: call model.eval() first "
+                               "(train-mode statistics are the zero-shot training path, Network._loss)")
         with torch.no_grad():
             r = self.frame_engine().infer(input, self.is_new_seq, self.last_H3, self.last_s3, self.of_scale)
         self.last_H3_wp, self.last_s3_wp = r["H3_wp"], r["s3_wp"]

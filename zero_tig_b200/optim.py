@@ -82,6 +82,10 @@ class ClipAdam:
         self.step_count += 1
         ops.clip_adam(self.flat, self.grad, self.exp_avg, self.exp_avg_sq, self.sumsq, self.step_count, self.lr,
                       self.betas, self.eps, self.weight_decay, self.max_norm, scale)
+        # the kernel wrote the parameters through raw pointers (torch's _version did not move): tell the engines'
+        # packed-weight caches explicitly
+        from .engine import bump_param_generation
+        bump_param_generation(self.params)
         self._attach_grads()
 
     def grad_norm(self):

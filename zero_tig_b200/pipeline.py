@@ -35,8 +35,10 @@ class FramePipeline:
 
     def run(self, frames, emit, new_sequence=True):
         """frames: sequence of pinned host tensors [1,3,H,W] fp32 (one sequence, in order).
-        emit(i, H2_host, H3_host) is called in order once frame i's outputs are in host memory; the host
-        buffers are reused ``depth`` frames later."""
+        emit(i, H2_host, H3_host) is called in order once frame i's outputs are in host memory.  The two host
+        tensors are pinned staging buffers that are valid ONLY for the duration of the callback: the device->host
+        copy of a later frame is enqueued into the same buffers right after emit returns, so a consumer that keeps
+        them (an asynchronous PNG writer, a list) must copy them first."""
         for _ in self.steps(frames, emit, new_sequence):
             pass
 
