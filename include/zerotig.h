@@ -165,6 +165,9 @@ int zt_retinex_h5_f32(const float* H2, const float* s2, const float* d, int d_cs
                       float* s3, int64_t HW, float eps, void* stream);
 /* save_images quantisation, predict.py:57-61: clip(x*255,0,255) -> uint8 (truncate), HWC */
 int zt_quantize_u8_hwc(const float* x, uint8_t* out, int C, int64_t HW, void* stream);
+/* transforms.ToTensor on the device, dataloader/multi_read_data.py:86-87,131 (uint8 HWC image -> float NCHW, value/255
+ * with IEEE division: bit-identical to torch's): lets a caller upload the 8-bit frame (1/4 of the bytes) */
+int zt_u8_hwc_to_f32(const uint8_t* in, float* out, int C, int64_t HW, void* stream);
 
 /* ---- Retinex networks at full resolution: TMA-fed tcgen05 convolution over bf16 NHWC activations ----
  * Replaces the nn.Conv2d layers of Denoise_1 / Enhancer / Denoise_2 (model/model.py:24-28,40-44,74-81) in

@@ -63,6 +63,10 @@ def test_no_cpu_fallback(weights, tmp_path):
     ck = tmp_path / "w.pt"
     torch.save(weights, ck)
     m = Finetunemodel(synth.make_args(model_pretrain=str(ck)))
+    # train-mode BatchNorm is not what the inference engine computes (it folds the running statistics): refuse
+    with pytest.raises(RuntimeError, match="eval"):
+        m(torch.rand(1, 3, 64, 64))
+    m.eval()
     with pytest.raises(RuntimeError, match="CUDA"):
         m(torch.rand(1, 3, 64, 64))
 

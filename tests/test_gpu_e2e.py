@@ -119,10 +119,13 @@ def test_too_small_frame_is_refused(model_factory):
         m(x)
 
 
-@pytest.mark.parametrize("u8", [False, True])
-def test_frame_pipeline_matches_direct_calls(model_factory, u8):
-    """FramePipeline (pinned host frames in, host H2/H3 out, copies on side streams) returns, in order, exactly
-    what per-frame model calls return; the u8 variant equals predict.py:57-61's clip(x*255).astype(uint8)."""
+@pytest.mark.parametrize("u8,in_u8,graph", [(False, False, True), (True, False, True), (True, True, True),
+                                             (False, False, False)])
+def test_frame_pipeline_matches_direct_calls(model_factory, u8, in_u8, graph):
+    """FramePipeline (pinned host frames in, host H2/H3 out, copies on side streams, steady-state frames replayed as
+    one CUDA graph) returns, in order, exactly what per-frame eager model calls return; `quantize_u8` equals
+    predict.py:57-61's clip(x*255).astype(uint8); `input_u8` (8-bit HWC upload + ToTensor on the device) feeds the
+    model bit-identical frames."""
     from zero_tig_b200 import synth
     from zero_tig_b200.pipeline import FramePipeline
     H, W, n = 128, 160, 7
@@ -134,8 +137,12 @@ def test_frame_pipeline_matches_direct_calls(model_factory, u8):
         H2, H3, _ = a(clip[t:t + 1].cuda())
         want.append((H2.cpu(), H3.cpu()))
     got = {}
-    pipe = FramePipeline(b, H, W, depth=2, quantize_u8=u8)
-    frames = [clip[t:t + 1].pin_memory() for t in range(n)]
+    pipe = FramePipeline(b, H, W, depth=2, quantize_u8=u8, input_u8=in_u8, graph=graph)
+    if in_u8:
+        frames = [(clip[t].permute(1, 2, 0) * 255.0).round().to(torch.uint8).contiguous().pin_memory() for t in range(n)]
+        assert torch.equal(frames[3].float().div(255).permute(2, 0, 1), clip[3])      # ToTensor round trip is exact
+    else:
+        frames = [clip[t:t + 1].pin_memory() for t in range(n)]
     pipe.run(frames, lambda i, h2, h3: got.__setitem__(i, (h2.clone(), h3.clone())))
     assert sorted(got) == list(range(n))
     for t in range(n):
@@ -145,6 +152,28 @@ def test_frame_pipeline_matches_direct_calls(model_factory, u8):
                 assert g_.shape == (H, W, 3) and np.array_equal(g_.numpy(), ref), t
             else:
                 assert torch.equal(g_, w_), t
+    with pytest.raises(ValueError):
+        pipe.run([torch.zeros(2, 2)], lambda *a_: None)
+
+
+def test_u8_converters_bit_exact():
+    """zt_u8_hwc_to_f32 == transforms.ToTensor (value / 255, true division) and zt_quantize_u8_hwc ==
+    clip(x*255, 0, 255).astype(uint8) (predict.py:57-61), vector and scalar paths."""
+    from zero_tig_b200 import ops
+    g = torch.Generator().manual_seed(2)
+    for H, W in ((16, 16), (5, 7)):                 # HW % 4 == 0 -> x4 kernels, else scalar kernels
+        img = torch.randint(0, 256, (H, W, 3), generator=g, dtype=torch.uint8)
+        if H == 16:
+            img.view(-1)[:256] = torch.arange(256, dtype=torch.uint8)
+        out = torch.empty(1, 3, H, W, device="cuda")
+        ops.u8_hwc_to_f32(img.cuda(), out, 3, H * W)
+        assert torch.equal(out.cpu()[0], img.float().div(255).permute(2, 0, 1))
+        x = torch.rand(1, 3, H, W, generator=g) * 1.2 - 0.1
+        x.view(-1)[:4] = torch.tensor([0.0, 1.0, 254.999 / 255, 1.0 / 255])
+        q = torch.empty(H, W, 3, dtype=torch.uint8, device="cuda")
+        ops.quantize_u8_hwc(x.cuda(), q, 3, H * W)
+        ref = np.clip(x[0].numpy().transpose(1, 2, 0) * 255.0, 0, 255.0).astype("uint8")
+        assert np.array_equal(q.cpu().numpy(), ref)
 
 
 @pytest.mark.parametrize("H,W,dataset,n", [(1080, 1920, "RLV", 3), (2160, 3840, "underwater", 2)])

@@ -71,6 +71,7 @@ SIGNATURES = {
     "zt_retinex_h2_f32": [P, P, I, P, P, L, F, P],
     "zt_retinex_h5_f32": [P, P, P, I, P, P, L, F, P],
     "zt_quantize_u8_hwc": [P, P, I, L, P],
+    "zt_u8_hwc_to_f32": [P, P, I, L, P],
     "zt_bn_train_nhwc_f32": [P, I, P, I, P, I, P, P, P, P, P, I, I, F, F, P],
     "zt_pair_downsample_f32": [P, P, P, I, I, I, F, P],
     "zt_sub_clamp_f32": [P, F, P, I, P, I, L, F, F, I, P],

@@ -198,6 +198,41 @@ __global__ void __launch_bounds__(256) quantize_u8_hwc_kernel(const float* __res
     }
 }
 
+// three channels, four pixels per thread: float4 plane loads, 12 contiguous output bytes (three 32-bit stores)
+__global__ void __launch_bounds__(256) quantize_u8_hwc3_x4_kernel(const float* __restrict__ x, uint32_t* __restrict__ out,
+                                                                  int64_t HW) {
+  const int64_t n4 = HW >> 2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 r = __ldg(reinterpret_cast<const float4*>(x) + i);
+    const float4 g = __ldg(reinterpret_cast<const float4*>(x + HW) + i);
+    const float4 b = __ldg(reinterpret_cast<const float4*>(x + 2 * HW) + i);
+    auto q = [](float v) { return (uint32_t)(int)fminf(fmaxf(v * 255.f, 0.f), 255.f); };
+    const uint32_t by[12] = {q(r.x), q(g.x), q(b.x), q(r.y), q(g.y), q(b.y), q(r.z), q(g.z), q(b.z), q(r.w), q(g.w), q(b.w)};
+    uint32_t* o = out + i * 3;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) o[k] = by[4 * k] | (by[4 * k + 1] << 8) | (by[4 * k + 2] << 16) | (by[4 * k + 3] << 24);
+  }
+}
+
+// ToTensor (dataloader/multi_read_data.py:86-87,131): uint8 HWC -> float NCHW, value / 255 (IEEE division, like torch)
+__global__ void __launch_bounds__(256) u8_hwc_to_f32_kernel(const uint8_t* __restrict__ in, float* __restrict__ out, int C,
+                                                            int64_t HW) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < HW; p += (int64_t)gridDim.x * blockDim.x)
+    for (int c = 0; c < C; ++c) out[c * HW + p] = __fdiv_rn((float)in[p * C + c], 255.f);
+}
+__global__ void __launch_bounds__(256) u8_hwc3_to_f32_x4_kernel(const uint32_t* __restrict__ in, float* __restrict__ out,
+                                                                int64_t HW) {
+  const int64_t n4 = HW >> 2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint32_t w0 = __ldg(in + i * 3), w1 = __ldg(in + i * 3 + 1), w2 = __ldg(in + i * 3 + 2);
+    auto f = [](uint32_t v) { return __fdiv_rn((float)(v & 255u), 255.f); };
+    // bytes: r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
+    reinterpret_cast<float4*>(out)[i] = make_float4(f(w0), f(w0 >> 24), f(w1 >> 16), f(w2 >> 8));
+    reinterpret_cast<float4*>(out + HW)[i] = make_float4(f(w0 >> 8), f(w1), f(w1 >> 24), f(w2 >> 16));
+    reinterpret_cast<float4*>(out + 2 * HW)[i] = make_float4(f(w0 >> 16), f(w1 >> 8), f(w2), f(w2 >> 24));
+  }
+}
+
 static inline int ew_blocks(int64_t n) { return (int)std::min<int64_t>(ceil_div64(n, 256), 16 * kNumSMs); }
 
 }  // namespace zt
@@ -271,6 +306,21 @@ extern "C" int zt_retinex_h5_f32(const float* H2, const float* s2, const float* 
 extern "C" int zt_quantize_u8_hwc(const float* x, uint8_t* out, int C, int64_t HW, void* stream) {
   using namespace zt;
   ZT_REQUIRE(x && out && C >= 1 && HW > 0, "quantize_u8: bad args");
+  if (C == 3 && (HW & 3) == 0 && (((uintptr_t)x | (uintptr_t)out) & 15) == 0) {
+    quantize_u8_hwc3_x4_kernel<<<ew_blocks(HW >> 2), 256, 0, (cudaStream_t)stream>>>(x, (uint32_t*)out, HW);
+    return check_launch("quantize_u8_hwc3_x4_kernel");
+  }
   quantize_u8_hwc_kernel<<<ew_blocks(HW), 256, 0, (cudaStream_t)stream>>>(x, out, C, HW);
   return check_launch("quantize_u8_hwc_kernel");
+}
+
+extern "C" int zt_u8_hwc_to_f32(const uint8_t* in, float* out, int C, int64_t HW, void* stream) {
+  using namespace zt;
+  ZT_REQUIRE(in && out && C >= 1 && HW > 0, "u8_hwc_to_f32: bad args");
+  if (C == 3 && (HW & 3) == 0 && (((uintptr_t)in | (uintptr_t)out) & 15) == 0) {
+    u8_hwc3_to_f32_x4_kernel<<<ew_blocks(HW >> 2), 256, 0, (cudaStream_t)stream>>>((const uint32_t*)in, out, HW);
+    return check_launch("u8_hwc3_to_f32_x4_kernel");
+  }
+  u8_hwc_to_f32_kernel<<<ew_blocks(HW), 256, 0, (cudaStream_t)stream>>>(in, out, C, HW);
+  return check_launch("u8_hwc_to_f32_kernel");
 }

@@ -114,6 +114,20 @@ class Finetunemodel(nn.Module, _Recurrent):
         self.update_H3(r["H3"], r["s3"])
         return r["H2"], r["H3"], r["s3"]
 
+    def forward_graphed(self, input):
+        """Beyond the reference interface (used by zero_tig_b200.pipeline): ``forward`` for a steady-state frame
+        (``is_new_seq`` False) whose input lives in a STATIC device buffer, replayed as one CUDA graph.  Same
+        results as ``forward``; the returned tensors are static buffers that the next call overwrites."""
+        if self.enhance.training:
+            raise RuntimeError("Finetunemodel.forward_graphed runs eval-mode BatchNorm only: call model.eval() first")
+        if self.is_new_seq or self.last_H3 is None:
+            return self.forward(input)
+        with torch.no_grad():
+            r = self.frame_engine().infer_graphed(input, self.last_H3, self.last_s3, self.of_scale)
+        self.last_H3_wp, self.last_s3_wp = r["H3_wp"], r["s3_wp"]
+        self.update_H3(r["H3"], r["s3"])
+        return r["H2"], r["H3"], r["s3"]
+
 
 class Network(nn.Module, _Recurrent):
     """Zero-shot training model (model/model.py:84-259): parameter tree, recurrent state,

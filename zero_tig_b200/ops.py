@@ -320,6 +320,11 @@ def quantize_u8_hwc(x, out, Cn, HW):
     check(lib().zt_quantize_u8_hwc(_p(x), _p(out), Cn, HW, _stream()), "quantize_u8")
 
 
+def u8_hwc_to_f32(img_u8, out, Cn, HW):
+    """transforms.ToTensor on the device: uint8 HWC -> float NCHW / 255 (multi_read_data.py:86-87,131)."""
+    check(lib().zt_u8_hwc_to_f32(_p(img_u8), _p(out), Cn, HW, _stream()), "u8_hwc_to_f32")
+
+
 # ---------------------------------------------------------------------------------------
 # training path (csrc/train.cu, csrc/norm_f32.cu)
 # ---------------------------------------------------------------------------------------
