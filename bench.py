@@ -318,7 +318,13 @@ def classify(c, frame_pixels):
                                     " +residual" if res is not None else "")
         return "conv_tma (TMA-fed tcgen05, bf16 activations)", flops, flops, byt, lab
     if name == "raft_update":
-        return "raft_update (persistent tcgen05 update block)", c.get("flops", 0.0), 3.0 * c.get("flops", 0.0), 0.0, "12 iterations"
+        h8, w8, iters, weights = a[0], a[1], a[2], a[8]
+        N = h8 * w8
+        per_iter = sum(2.0 * N * w.w_raw.shape[0] * w.w_raw.shape[1] * w.kh * w.kw for w in weights)   # the 9 tensor-core layers
+        cuda_core = 2.0 * N * (128 * 98 + 2 * 2304)                       # convf1 + flow-head conv2 (fp32 FFMA)
+        byt = iters * N * (324 * 4 + 4 * 100 * 4 + 8.0)                    # lookup traffic, for reference
+        return ("raft_update (persistent TMA-fed tcgen05 update block, all %d iterations)" % iters,
+                iters * (per_iter + cuda_core), 3.0 * iters * per_iter, byt, "%d iterations @%dx%d" % (iters, h8, w8))
     if name == "warp_pair":
         flow, hf, wf = a[0], a[1], a[2]
         Cn, Hn, Wn = a[7], a[8], a[9]
@@ -412,6 +418,9 @@ def run_b200(args):
     S = max(1, int(os.environ.get("ZT_SHARDS_PER_GPU", "3" if args.config == "1080p" else "1")))
     sd = synthetic_weights()
     models = [build_model(dev, dataset, sd)[0] for _ in range(S)]
+    from zero_tig_b200.pipeline import share_sms
+    share_sms(models)            # S > 1: each replica's persistent RAFT kernel gets 148 // S CTAs (throughput mode)
+    solo = build_model(dev, dataset, sd)[0] if S > 1 else None      # full-grid replica for the single-sequence number
     K, Wm = args.steps, args.warmup
 
     # ---- the clip: 1080p = one 64-frame clip per rank; uw4k = ONE clip cut into `world` frame ranges (+ halo) ----
@@ -444,12 +453,13 @@ def run_b200(args):
 
     pos = [0] * S
 
-    def step_dev(s):
+    def step_dev(s, m=None):
         f = steady[s][pos[s] % len(steady[s])]
         pos[s] += 1
+        m = m or models[s]
         with torch.cuda.stream(streams[s]):
-            models[s].is_new_seq = False
-            return models[s](clip[f:f + 1])
+            m.is_new_seq = False
+            return m(clip[f:f + 1])
 
     def region(shards, k):
         """k steady-state frames round-robin over `shards` shards; device time from the fork to the join."""
@@ -461,7 +471,7 @@ def run_b200(args):
         for s in range(shards):
             streams[s].wait_event(e0)
         for i in range(k):
-            step_dev(i % shards)
+            step_dev(i % shards, solo if (shards == 1 and solo is not None) else None)
         for s in range(shards):
             ev = torch.cuda.Event()
             ev.record(streams[s])
@@ -480,6 +490,12 @@ def run_b200(args):
             models[s](clip[ranges[s][0]:ranges[s][0] + 1])      # seed frame (new sequence / halo), never timed
     for i in range(Wm * S):
         step_dev(i % S)
+    if solo is not None:                                        # the lone-sequence replica (full SM grid)
+        with torch.cuda.stream(streams[0]):
+            solo.is_new_seq = True
+            solo(clip[ranges[0][0]:ranges[0][0] + 1])
+        for i in range(Wm):
+            step_dev(0, solo)
     first_ms, launches = region(S, K)
     R = reps_for(first_ms)
     if world > 1:
@@ -586,12 +602,13 @@ def run_b200(args):
             "shards_per_gpu": S,
             "single_shard": None if single_ms is None else {
                 "value": fps(statistics.median(single_ms)), "unit": UNIT, "ms_per_step": statistics.median(single_ms) / K,
-                "note": "one shard alone on the GPU = the strictly sequential per-clip latency path; same K frames, device-timed"},
+                "note": "one sequence alone on the GPU = the strictly sequential per-clip latency path (the persistent RAFT "
+                        "kernel on the full SM grid); same K frames, device-timed"},
             "gpu_launches": int(launches),
         }
         if not args.no_profile:
             step_us = (statistics.median(single_ms) if single_ms else med) / K * 1e3     # one chain alone
-            fams, rows = profile_frame(models[0], clip[steady[0][0]:steady[0][0] + 1], pk, H * W)
+            fams, rows = profile_frame(solo or models[0], clip[steady[0][0]:steady[0][0] + 1], pk, H * W)
             order = sorted(fams.items(), key=lambda kv: -kv[1]["us"])
             tensor_f = [(n, f) for n, f in order if f["issued"] > 0]
             hbm_f = [(n, f) for n, f in order if f["issued"] == 0 and f["bytes"] > 0]

@@ -71,15 +71,21 @@ typedef struct ZtConv {
   const float* bplane; int bplane_cs;   /* optional per-pixel bias [M][bplane_cs] added before the epilogue (tensor-core
                                           path only): the iteration-invariant part of a GRU convolution, i.e. the
                                           convolution of the context features `inp` (update.py:47,50), computed once per frame */
+  float acc_scale;                     /* tensor-core split mode 4 only: 1 / (ZT_F16_ACT_SCALE * weight scale) */
 } ZtConv;
 int zt_conv2d_nhwc_f32(const ZtConv* d, void* stream);
 
 /* Same convolution on the tcgen05 tensor cores (stride 1 only): `weight` points at bf16 hi/lo
  * weights packed by the host as [n_tile][64-ch group][tap][hi|lo][row BN][64 ch], every
  * 128-byte row stored with the UMMA 128B swizzle (16 B chunk c of row n at position c^(n&7)),
- * zero padded; w_cs is ignored.  split = 1: bf16 x bf16; split = 3: hi*hi + lo*hi + hi*lo
- * (about 2^-16 relative, needed for RAFT's 0.01 px tolerance).  BN = N tile, multiple of 16
+ * zero padded; w_cs is ignored.  split = 1: bf16 x bf16; split = 3: hi*hi + lo*hi + hi*lo over bf16 pairs
+ * (about 2^-17 relative per operand, what RAFT's 0.01 px tolerance needs); split = 4: the same three products
+ * over fp16 hi/lo pairs of the SCALED operands - activations * ZT_F16_ACT_SCALE (applied by the kernel), weights *
+ * a power of two chosen by the packer so that the low halves stay normal fp16 numbers - about 2^-22 per operand,
+ * i.e. fp32-grade; the accumulator is multiplied by desc.acc_scale = 1 / (both scales) before the epilogue.  An
+ * activation above 65504 / ZT_F16_ACT_SCALE would overflow to inf (loud, not silent).  BN = N tile, multiple of 16
  * in [16,256].  Same call sites as zt_conv2d_nhwc_f32. */
+#define ZT_F16_ACT_SCALE 16.0f
 int zt_conv2d_tc_nhwc(const ZtConv* d, int BN, int split, void* stream);
 
 /* Pack R rows x C fp32 (row stride rs) as the weight operand of zt_conv2d_tc_nhwc for a 1x1
@@ -112,10 +118,18 @@ int zt_avgpool2_f32(const float* in, float* out, int64_t planes, int h, int w, v
 int64_t zt_corr_pyramid_scratch_bytes(int h0, int w0);
 int zt_corr_pyramid_f32(const float* fmap, int fm_rs, int h0, int w0, float* l0, float* l1, float* l2,
                         float* l3, void* scratch, int64_t scratch_bytes, void* stream);
+/* bf16-STORAGE variant (BASELINE.json configs[4], "fp32 vs bf16 corr"): the same GEMM (fp32-grade products, fp32
+ * accumulation); the four levels are rounded to bf16 on the way out, halving the bytes of this output-bound kernel */
+int zt_corr_pyramid_bf16(const float* fmap, int fm_rs, int h0, int w0, void* l0, void* l1, void* l2,
+                         void* l3, void* scratch, int64_t scratch_bytes, void* stream);
 /* CorrBlock.__call__ (corr.py:29-50) + bilinear_sampler (utils/utils.py:285-299):
  * coords [N][2] (x,y), pyramid level l is [N][hl][wl]; out [N][out_cs], channel
  * l*81 + a*9 + b samples level l at (x/2^l + a-4, y/2^l + b-4)  (x-offset major). */
 int zt_corr_lookup_f32(const float* l0, const float* l1, const float* l2, const float* l3,
+                       const int* hs, const int* ws_, /* host arrays[4] */
+                       const float* coords, float* out, int out_cs, int N, void* stream);
+/* the same lookup over a bf16-storage pyramid (zt_corr_pyramid_bf16); interpolation and output stay fp32 */
+int zt_corr_lookup_bf16(const void* l0, const void* l1, const void* l2, const void* l3,
                        const int* hs, const int* ws_, /* host arrays[4] */
                        const float* coords, float* out, int out_cs, int N, void* stream);
 /* RAFT.upsample_flow (raft.py:64-75): flow [N][flow_cs] NHWC (first 2 channels), mask [N][576]
@@ -205,6 +219,46 @@ int zt_conv3x3_n2_f32(const float* in, int in_cs, int C, const float* weight, co
  * conv3x3(in); flow = coords1 - pixel grid is written to f1 / f2 (NHWC, first 2 channels; either may be NULL) */
 int zt_flow_head2_update_f32(const float* in, int in_cs, int C, const float* weight, const float* bias,
                              float* coords1, float* f1, int f1_cs, float* f2, int f2_cs, int H, int W, void* stream);
+
+/* ---- RAFT update block, all iterations of a frame pair in ONE persistent cooperative kernel ----
+ * Replaces the loop body of RAFT.forward, model/RAFT/raft.py:111-120: CorrBlock.__call__ (corr.py:29-50),
+ * BasicUpdateBlock.forward (update.py:127-136: BasicMotionEncoder :89-97, SepConvGRU :45-60, FlowHead :13-14) and
+ * coords1 += delta_flow, for `iters` iterations (the convex-upsampling mask head runs once afterwards, Q15).
+ * Every activation that feeds a convolution is a pair of 16-bit tensors [N][C] (hi, lo: bf16 with hi + lo = the fp32
+ * value to 2^-17, or - fp16 != 0 - fp16 of the value * ZT_F16_ACT_SCALE, to 2^-22), N = h8*w8 positions, so TMA can
+ * feed the tensor cores; products use the three-term hi/lo split.
+ *   in : h [N][128] fp32 hidden state (tanh(cnet[:128]), raft.py:104), the four per-frame GRU planes
+ *        bp_* = conv_{z|r,q}(context features) + bias (the iteration-invariant share of update.py:47-58),
+ *        the 4-level correlation pyramid lvl[i] = [N][lh[i]*lw[i]] fp32
+ *   out: flow4 [N][4] fp32 (flow in channels 0,1 = coords1 - coords0), coords1 [N][2], h (final hidden state)
+ * Weights: w[i] = bf16 hi/lo packed as for zt_conv2d_tc_nhwc with N tile bn[i] (32 or 64), b[i] fp32 bias or NULL,
+ * layer order convc1, convf2, convc2, conv, zr1, q1, zr2, q2, flow-head conv1; the GRU weights are the [h | motion]
+ * input-channel slices (the context slice lives in bp_*).  wf1 / bf1: convf1 fp32 [7][7][2][128] / [128];
+ * wfh2 / bfh2: flow-head conv2 fp32 [9][256][2] / [2].  corr_* [N][384] must have channels 324..383 zero.
+ * counter: one device word for the grid barrier (the call zeroes it).  max_ctas: 0 = as many as fit. */
+typedef struct ZtRaftUpdate {
+  int h8; int w8; int iters; int max_ctas;
+  void *corr_hi, *corr_lo;      /* [N][384] */
+  void *c1_hi, *c1_lo;          /* [N][256] */
+  void *f1_hi, *f1_lo;          /* [N][128] */
+  void *c2f_hi, *c2f_lo;        /* [N][256] */
+  void *hm_hi, *hm_lo;          /* [N][256]: hidden state | motion features */
+  void *rh_hi, *rh_lo;          /* [N][128] */
+  float *h, *z, *fhid, *coords1, *flow4;
+  const float *bp_zr1, *bp_q1, *bp_zr2, *bp_q2;
+  const void* lvl[4]; int lh[4]; int lw[4]; int lvl_bf16;   /* pyramid planes fp32, or bf16 when lvl_bf16 != 0 */
+  const void* w[9]; const float* b[9]; int bn[9];
+  int fp16; float acc_scale[9];  /* fp16 != 0: split mode 4 of zt_conv2d_tc_nhwc (scaled fp16 hi/lo operands, weights packed
+                                    accordingly, acc_scale[i] = 1 / (ZT_F16_ACT_SCALE * weight scale of layer i)) */
+  const float *wf1, *bf1, *wfh2, *bfh2;
+  unsigned int* counter;
+} ZtRaftUpdate;
+int zt_raft_update(const ZtRaftUpdate* desc, void* stream);
+/* debug only: device buffer of 8 * (2 + 9*iters) int64; CTA `cta` of the following zt_raft_update launches stores
+ * %globaltimer (ns) per phase and role (see ru_trace in csrc/raft_update.cu); NULL disables */
+int zt_debug_set_raft_update_trace(void* buf, int cta);
+/* fp32 [N][C] (row stride in_rs) -> bf16 hi / lo [N][C] (row stride out_rs), hi = bf16(x), lo = bf16(x - hi) */
+int zt_split_bf16_hilo(const float* in, int in_rs, void* hi, void* lo, int out_rs, int C, int64_t N, void* stream);
 
 /* ---- training path: Network.forward (model/model.py:144-203) and loss.py -------------------
  * NCHW fp32, batch 1.  Reduction entry points ADD raw sums into fp64 accumulators the caller

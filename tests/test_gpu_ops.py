@@ -207,6 +207,33 @@ def test_corr_pyramid_fused_vs_oracle(dev, h, w):
             assert (got - ref).abs().max().item() < 5e-5, (i, (got - ref).abs().max().item())
 
 
+@pytest.mark.parametrize("h,w", [(16, 16), (17, 23), (45, 80)])
+def test_corr_pyramid_bf16_storage_is_the_rounded_fp32_pyramid(dev, h, w):
+    """zt_corr_pyramid_bf16 (configs[4] "bf16 corr"): same GEMM, levels rounded to bf16 on the way out - every entry
+    is within one bf16 rounding (2^-9 relative) of the fp32-storage kernel's, and the bf16 lookup returns exactly the
+    fp32 lookup of those rounded planes."""
+    from zero_tig_b200 import ops
+    g = torch.Generator().manual_seed(h + w)
+    f1 = torch.randn(1, 256, h, w, generator=g)
+    f2 = torch.randn(1, 256, h, w, generator=g)
+    lv, hs, ws = _fused_pyramid(f1, f2, dev)
+    N = h * w
+    fmap = torch.cat([nhwc(f1), nhwc(f2)], 0).contiguous()
+    lb = [torch.full((N, max(hs[i] * ws[i], 1)), float("nan"), device=dev).to(torch.bfloat16) for i in range(4)]
+    scratch = torch.empty(ops.corr_pyramid_scratch_bytes(h, w) // 4, device=dev)
+    ops.corr_pyramid(fmap, 256, h, w, lb, scratch)
+    for i in range(4):
+        if hs[i] * ws[i]:
+            assert torch.isfinite(lb[i].float()).all()
+            assert torch.equal(lb[i], lv[i].to(torch.bfloat16)), i
+    if min(hs[3], ws[3]) >= 2:
+        coords = (torch.rand(N, 2, generator=g) * torch.tensor([w + 6.0, h + 6.0]) - 3).cuda()
+        a, b = torch.empty(N, 324, device=dev), torch.empty(N, 324, device=dev)
+        ops.corr_lookup(lb, hs, ws, coords, a, 324, N)
+        ops.corr_lookup([t.float() for t in lb], hs, ws, coords, b, 324, N)
+        assert torch.equal(a, b)
+
+
 def test_corr_pyramid_fused_rejects_bad_args(dev):
     from zero_tig_b200 import ops
     t = torch.zeros(64, device=dev)

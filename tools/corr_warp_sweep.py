@@ -2,7 +2,9 @@
 (frame sizes 256^2 .. 4K at of_scale 3, plus of_scale 1 for the small frames) against the HBM roofline.
 Algorithmic bytes per SURVEY 8d: volume+pyramid = 4*N^2*(1+1/4+1/16+1/64) written + 2*N*256*4 read;
 lookup = N*(324*4 + 4*100*4 + 8) per iteration; warp pair = flow + 2 planes read + 2 planes written.
-    python tools/corr_warp_sweep.py > profiles/r01_corr_warp_sweep.txt
+fp32 arm = the reference's storage; bf16 arm = zt_corr_pyramid_bf16 / zt_corr_lookup_bf16 (levels rounded to bf16 on
+the way out: 2*N^2*(1+1/4+1/16+1/64) bytes written).
+    python tools/corr_warp_sweep.py > profiles/r02_corr_warp_sweep.txt
 """
 import json
 import os
@@ -48,8 +50,9 @@ def main():
     g = torch.Generator().manual_seed(0)
     print("# HBM peak %.1f GB/s (measured copy bandwidth); times are CUDA-event averages, us" % PEAK)
     print("# corr3 = pack + conv_tc GEMM + 3 avgpool kernels (ZT_CORR_FUSED=0); corr = zt_corr_pyramid_f32 (pack + one tcgen05 kernel)")
-    print("%-22s %7s | %9s %9s %7s %6s | %9s %7s %6s | %9s %7s %6s" % ("frame (of_scale)", "N", "corr3 us", "corr us", "GB/s", "frac",
-                                                                      "lookup us", "GB/s", "frac", "warp us", "GB/s", "frac"))
+    print("%-22s %7s | %9s %9s %7s %6s | %9s %7s %6s | %9s %7s %6s | %9s %7s %6s | %9s" % (
+        "frame (of_scale)", "N", "corr3 us", "corr us", "GB/s", "frac", "lookup us", "GB/s", "frac", "warp us", "GB/s", "frac",
+        "corr16 us", "GB/s", "frac", "lookup16"))
     cases = [(256, 256, 1), (512, 512, 1), (540, 960, 3), (1080, 1920, 3), (1080, 1920, 1), (2160, 3840, 3)]
     for H, W, s in cases:
         ht, wd = H // s, W // s
@@ -87,11 +90,18 @@ def main():
         t_w = timed(lambda: ops.warp_pair(flow, hp, wp, a, b, oa, ob, 3, H, W))
         b_w = 2.0 * hp * wp * 4 + 4.0 * 3 * H * W * 4
         r = lambda byt, us: (byt / us / 1e3, byt / us / 1e3 / PEAK)
-        print("%-22s %7d | %9.1f %9.1f %7.0f %6.3f | %9.1f %7.0f %6.3f | %9.1f %7.0f %6.3f" % (
-            "%dx%d (%d)" % (H, W, s), N, t_c3, t_c, *r(b_c, t_c), t_l, *r(b_l, t_l), t_w, *r(b_w, t_w)), flush=True)
-        del fmap, lv, cw, scratch
+        # bf16-storage arm
+        lb = [torch.empty(N, hs[i] * ws_[i], device="cuda", dtype=torch.bfloat16) for i in range(4)]
+        t_c16 = timed(lambda: ops.corr_pyramid(fmap, 256, h8, w8, lb, scratch))
+        b_c16 = 2.0 * N * sum(hs[i] * ws_[i] for i in range(4)) + 2.0 * N * 256 * 4
+        t_l16 = timed(lambda: ops.corr_lookup(lb, hs, ws_, coords, out, 324, N), 20)
+        print("%-22s %7d | %9.1f %9.1f %7.0f %6.3f | %9.1f %7.0f %6.3f | %9.1f %7.0f %6.3f | %9.1f %7.0f %6.3f | %9.1f" % (
+            "%dx%d (%d)" % (H, W, s), N, t_c3, t_c, *r(b_c, t_c), t_l, *r(b_l, t_l), t_w, *r(b_w, t_w),
+            t_c16, *r(b_c16, t_c16), t_l16), flush=True)
+        del fmap, lv, lb, cw, scratch
         torch.cuda.empty_cache()
-    print("# correlation volume is stored fp32 (the reference's layout); a bf16-storage variant is not built")
+    print("# corr / lookup = fp32 storage (the reference's layout); corr16 / lookup16 = bf16 storage (same GEMM, levels rounded on "
+          "the way out).  Timed with CUDA-graph replay of back-to-back calls: inputs of the small sizes are L2-resident.")
 
 
 if __name__ == "__main__":

@@ -25,6 +25,7 @@ class ZtConv(C.Structure):
         ("aux0", c_fp), ("aux0_cs", C.c_int),
         ("aux1", c_fp), ("aux1_cs", C.c_int),
         ("bplane", c_fp), ("bplane_cs", C.c_int),
+        ("acc_scale", C.c_float),
     ]
 
 
@@ -37,6 +38,15 @@ class ZtConvBf16(C.Structure):
         ("H", C.c_int), ("W", C.c_int), ("cout", C.c_int), ("kh", C.c_int), ("kw", C.c_int), ("act", C.c_int),
         ("head_w", c_fp), ("head_b", c_fp), ("head_n", C.c_int),
     ]
+
+
+class ZtRaftUpdate(C.Structure):
+    _fields_ = ([("h8", C.c_int), ("w8", C.c_int), ("iters", C.c_int), ("max_ctas", C.c_int)] +
+                [(n + s, c_fp) for n in ("corr", "c1", "f1", "c2f", "hm", "rh") for s in ("_hi", "_lo")] +
+                [(n, c_fp) for n in ("h", "z", "fhid", "coords1", "flow4", "bp_zr1", "bp_q1", "bp_zr2", "bp_q2")] +
+                [("lvl", c_fp * 4), ("lh", C.c_int * 4), ("lw", C.c_int * 4), ("lvl_bf16", C.c_int),
+                 ("w", c_fp * 9), ("b", c_fp * 9), ("bn", C.c_int * 9), ("fp16", C.c_int), ("acc_scale", C.c_float * 9)] +
+                [(n, c_fp) for n in ("wf1", "bf1", "wfh2", "bfh2", "counter")])
 
 
 I, L, F, P = C.c_int, C.c_int64, C.c_float, C.c_void_p
@@ -53,11 +63,16 @@ SIGNATURES = {
     "zt_raft_convf1_f32": [P, I, P, P, P, I, I, I, P],
     "zt_conv3x3_n2_f32": [P, I, I, P, P, P, I, I, I, P],
     "zt_flow_head2_update_f32": [P, I, I, P, P, P, P, I, P, I, I, I, P],
+    "zt_raft_update": [C.POINTER(ZtRaftUpdate), P],
+    "zt_debug_set_raft_update_trace": [P, I],
+    "zt_split_bf16_hilo": [P, I, P, P, I, I, L, P],
     "zt_pack_tc_rows_f32": [P, I, I, I, I, P, P],
     "zt_instnorm_nhwc_f32": [P, I, P, I, P, I, P, I, I, I, F, I, I, P],
     "zt_transpose_f32": [P, I, I, I, P, I, P],
     "zt_avgpool2_f32": [P, P, L, I, I, P],
     "zt_corr_lookup_f32": [P, P, P, P, IP, IP, P, P, I, I, P],
+    "zt_corr_lookup_bf16": [P, P, P, P, IP, IP, P, P, I, I, P],
+    "zt_corr_pyramid_bf16": [P, I, I, I, P, P, P, P, P, L, P],
     "zt_corr_pyramid_scratch_bytes": [I, I],
     "zt_corr_pyramid_f32": [P, I, I, I, P, P, P, P, P, L, P],
     "zt_convex_upsample_f32": [P, I, P, I, P, I, I, P],

@@ -22,6 +22,7 @@
 // Replaces nn.Conv2d call sites with stride 1: model/model.py:24-28,40-44,74-81;
 // model/RAFT/update.py:13-14,45-60,89-97,127-136; model/RAFT/extractor.py:46-55,167-191.
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdlib.h>
 #include <algorithm>
 #include "common.cuh"
@@ -59,6 +60,9 @@ struct TcGeom {
                      // owns a single pixel tile: the ring is dead once the accumulator is complete)
   long long* trace;  // debug: per-role timestamps of CTA (0,0) (zt_debug_set_tc_trace), else NULL
   int trace_cap;
+  int fp16;          // split mode 4: operands are fp16 hi/lo pairs of the SCALED values (activation * ZT_F16_ACT_SCALE,
+                     // weight * per-layer power of two): 2^-22 per operand instead of the 2^-17 of the bf16 pair
+  float acc_scale;   // accumulator * acc_scale = the unscaled convolution sum (1 unless fp16)
 };
 
 // debug timeline: record (event, index, globaltimer ns) for CTA (0,0); every role (warp) owns a
@@ -93,6 +97,17 @@ __device__ __forceinline__ void split4(const float4 v, uint2& hi, uint2& lo) {
   hi.y = (uint32_t)__bfloat16_as_ushort(h2) | ((uint32_t)__bfloat16_as_ushort(h3) << 16);
   lo.x = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
   lo.y = (uint32_t)__bfloat16_as_ushort(l2) | ((uint32_t)__bfloat16_as_ushort(l3) << 16);
+}
+
+// the same for split mode 4: 4 fp32 (already multiplied by the activation scale) -> 4 fp16 hi + 4 fp16 lo
+__device__ __forceinline__ void split4h(const float4 v, uint2& hi, uint2& lo) {
+  const __half h0 = __float2half_rn(v.x), h1 = __float2half_rn(v.y), h2 = __float2half_rn(v.z), h3 = __float2half_rn(v.w);
+  const __half l0 = __float2half_rn(v.x - __half2float(h0)), l1 = __float2half_rn(v.y - __half2float(h1));
+  const __half l2 = __float2half_rn(v.z - __half2float(h2)), l3 = __float2half_rn(v.w - __half2float(h3));
+  hi.x = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
+  hi.y = (uint32_t)__half_as_ushort(h2) | ((uint32_t)__half_as_ushort(h3) << 16);
+  lo.x = (uint32_t)__half_as_ushort(l0) | ((uint32_t)__half_as_ushort(l1) << 16);
+  lo.y = (uint32_t)__half_as_ushort(l2) | ((uint32_t)__half_as_ushort(l3) << 16);
 }
 
 // ---------------------------------------------------------------- epilogue
@@ -278,7 +293,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
           uint32_t v2[16];
           tmem_ld16(taddr + (uint32_t)g.BN, v2);
 #pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(v2[i]));
+          for (int i = 0; i < 16; ++i) v[i] = __float_as_uint((__uint_as_float(v[i]) + __uint_as_float(v2[i])) * g.acc_scale);
         }
 #pragma unroll
         for (int i = 0; i < 4; ++i)
@@ -289,7 +304,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
             uint32_t v2[16];
             tmem_ld16(taddr + 16 + (uint32_t)g.BN, v2);
 #pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(v2[i]));
+            for (int i = 0; i < 16; ++i) v[i] = __float_as_uint((__uint_as_float(v[i]) + __uint_as_float(v2[i])) * g.acc_scale);
           }
 #pragma unroll
           for (int i = 0; i < 4; ++i)
@@ -352,10 +367,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
     // ===================== MMA issuer (whole warp converged, one elected lane issues) ==========
     {
       const uint32_t BN = g.BN, PW = g.PW, kh = d.kh, kw = d.kw;
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((BN >> 3) << 17) | (8u << 24);
+      // operand formats of kind::f16: 1 = bf16 (default), 0 = fp16 (split mode 4)
+      const uint32_t fmt = g.fp16 ? 0u : ((1u << 7) | (1u << 10));
+      const uint32_t idesc = (1u << 4) | fmt | ((BN >> 3) << 17) | (8u << 24);
       // SPLIT=3: the hi and lo weight blocks of a stage are contiguous rows of one swizzled matrix, so
       // Ahi * [Bhi | Blo] is ONE MMA with N = 2*BN (A is fetched once); Alo * Bhi is the second
-      const uint32_t idesc2 = (1u << 4) | (1u << 7) | (1u << 10) | ((BN >> 2) << 17) | (8u << 24);
+      const uint32_t idesc2 = (1u << 4) | fmt | ((BN >> 2) << 17) | (8u << 24);
       const uint32_t accw = (SPLIT == 3 ? 2u : 1u) * BN;
       // descriptor templates: only the 14-bit start-address field (16 B units) changes per MMA;
       // a K step of 16 channels is +32 B inside the swizzled 128 B row
@@ -529,7 +546,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const ZtConv d, 
         const int p = p0 + 16 * u;
         if (p < P) {
           uint2 hi, lo;
-          split4(v[u], hi, lo);
+          if (SPLIT == 3 && g.fp16) {
+            const float4 t = v[u];
+            split4h(make_float4(t.x * ZT_F16_ACT_SCALE, t.y * ZT_F16_ACT_SCALE, t.z * ZT_F16_ACT_SCALE, t.w * ZT_F16_ACT_SCALE), hi, lo);
+          } else {
+            split4(v[u], hi, lo);
+          }
           // 128B swizzle: 16 B chunk (q>>1) of row p lives at chunk position (q>>1) ^ (p & 7)
           const uint32_t off = (uint32_t)p * 128u + ((uint32_t)((q >> 1) ^ (p & 7)) << 4) + (uint32_t)(q & 1) * 8u;
           *reinterpret_cast<uint2*>(dst_hi + off) = hi;
@@ -637,7 +659,11 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
   // correlation: weights = fmap2 packed per frame), so it must not be fetched before that kernel completes
   const bool w_dynamic = (split & 0x100) != 0;
   split &= 0xff;
-  ZT_REQUIRE(split == 1 || split == 3, "conv_tc: split must be 1 (bf16) or 3 (bf16 hi/lo, 3 products); got %d", split);
+  ZT_REQUIRE(split == 1 || split == 3 || split == 4,
+             "conv_tc: split must be 1 (bf16), 3 (bf16 hi/lo, 3 products) or 4 (scaled fp16 hi/lo, 3 products); got %d", split);
+  const bool fp16 = split == 4;
+  if (fp16) split = 3;
+  ZT_REQUIRE(!fp16 || (d.acc_scale > 0.f && !w_dynamic), "conv_tc: split 4 needs acc_scale = 1 / (activation scale * weight scale) and host-packed weights");
   ZT_REQUIRE(BN >= 16 && BN <= 256 && (BN & 15) == 0, "conv_tc: BN=%d must be a multiple of 16 in [16,256]", BN);
   ZT_REQUIRE(d.sh == 1 && d.sw == 1, "conv_tc: stride-1 convolutions only (got %dx%d)", d.sh, d.sw);
   ZT_REQUIRE((d.c0 & 3) == 0 && (d.c1 & 3) == 0 && cin > 0, "conv_tc: channel counts must be multiples of 4 (c0=%d c1=%d)", d.c0, d.c1);
@@ -670,6 +696,8 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
   static const bool pdl_on = getenv("ZT_NO_PDL") == nullptr;
   g.pdl = pdl_on ? 1 : 0;
   g.w_early = w_dynamic ? 0 : 1;
+  g.fp16 = fp16 ? 1 : 0;
+  g.acc_scale = fp16 ? d.acc_scale : 1.f;
   g.tmem_cols = 32;
   ZT_REQUIRE(split == 1 || BN <= 128, "conv_tc: the hi/lo split keeps 2*BN accumulator columns, BN=%d > 128", BN);
   while (g.tmem_cols < (split == 3 ? 4 : 2) * BN) g.tmem_cols <<= 1;

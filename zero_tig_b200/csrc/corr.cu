@@ -1,5 +1,6 @@
 // RAFT correlation pyramid helpers, 4-level 9x9 bilinear lookup, convex upsampling.
 // Reference: model/RAFT/corr.py:13-60, utils/utils.py:285-299, model/RAFT/raft.py:64-75,111-120.
+#include <cuda_bf16.h>
 #include <algorithm>
 #include "common.cuh"
 
@@ -38,14 +39,19 @@ __global__ void avgpool2_kernel(const float* __restrict__ in, float* __restrict_
 
 // ---------------- 4-level lookup ----------------
 struct LookupArgs {
-  const float* lvl[4];
+  const void* lvl[4];    // fp32 or bf16 planes (template parameter of the kernel)
   int h[4], w[4];
 };
+__device__ __forceinline__ float lk_get(const float* p, int64_t i) { return __ldg(p + i); }
+__device__ __forceinline__ float lk_get(const __nv_bfloat16* p, int64_t i) {
+  return __bfloat162float(__ushort_as_bfloat16(__ldg(reinterpret_cast<const unsigned short*>(p) + i)));
+}
 
 // One WARP per query position (4 queries per 128-thread CTA, no block-wide barrier): per level the 10x10
 // window of the position's own correlation plane that covers the 9x9 bilinear taps is staged in shared memory
 // with zeros outside the plane (grid_sample padding_mode='zeros') - 12-13 independent loads in flight per lane -
 // then 324 outputs are written contiguously (channel-fastest NHWC, the layout convc1 consumes).
+template <typename T>
 __global__ void __launch_bounds__(128) corr_lookup_kernel(const LookupArgs a, const float* __restrict__ coords,
                                                           float* __restrict__ out, int out_cs, int N) {
   __shared__ float win_s[4][4][10][12];
@@ -70,9 +76,9 @@ __global__ void __launch_bounds__(128) corr_lookup_kernel(const LookupArgs a, co
       // selects instead of dynamic indexing: keeps the kernel parameters out of local memory
       const int hl = l == 0 ? a.h[0] : l == 1 ? a.h[1] : l == 2 ? a.h[2] : a.h[3];
       const int wl = l == 0 ? a.w[0] : l == 1 ? a.w[1] : l == 2 ? a.w[2] : a.w[3];
-      const float* pl = l == 0 ? a.lvl[0] : l == 1 ? a.lvl[1] : l == 2 ? a.lvl[2] : a.lvl[3];
+      const T* pl = reinterpret_cast<const T*>(l == 0 ? a.lvl[0] : l == 1 ? a.lvl[1] : l == 2 ? a.lvl[2] : a.lvl[3]);
       float v = 0.f;
-      if (ix >= 0 && ix < wl && iy >= 0 && iy < hl) v = __ldg(pl + ((int64_t)n * hl + iy) * wl + ix);
+      if (ix >= 0 && ix < wl && iy >= 0 && iy < hl) v = lk_get(pl, ((int64_t)n * hl + iy) * wl + ix);
       win[l][wy][wx] = v;
       if (r == 0) { frac[l][0] = x - fx0; frac[l][1] = y - fy0; }
     }
@@ -168,9 +174,8 @@ extern "C" int zt_avgpool2_f32(const float* in, float* out, int64_t planes, int 
   return check_launch("avgpool2_kernel");
 }
 
-extern "C" int zt_corr_lookup_f32(const float* l0, const float* l1, const float* l2, const float* l3,
-                                  const int* hs, const int* ws_, const float* coords, float* out, int out_cs,
-                                  int N, void* stream) {
+static int corr_lookup_any(const void* l0, const void* l1, const void* l2, const void* l3, bool lvl_bf16,
+                           const int* hs, const int* ws_, const float* coords, float* out, int out_cs, int N, void* stream) {
   using namespace zt;
   ZT_REQUIRE(l0 && l1 && l2 && l3 && hs && ws_ && coords && out && N > 0 && out_cs >= 324, "corr_lookup: bad args");
   LookupArgs a;
@@ -180,8 +185,23 @@ extern "C" int zt_corr_lookup_f32(const float* l0, const float* l1, const float*
     // the reference divides by (W-1), (H-1): a 1-pixel level is NaN there; refuse.
     ZT_REQUIRE(hs[i] >= 2 && ws_[i] >= 2, "corr_lookup: pyramid level %d is %dx%d; the reference yields NaN below 2x2", i, hs[i], ws_[i]);
   }
-  ZT_CUDA(launch_pdl(corr_lookup_kernel, dim3(ceil_div(N, 4)), dim3(128), 0, (cudaStream_t)stream, a, coords, out, out_cs, N));
+  if (lvl_bf16)
+    ZT_CUDA(launch_pdl(corr_lookup_kernel<__nv_bfloat16>, dim3(ceil_div(N, 4)), dim3(128), 0, (cudaStream_t)stream, a, coords, out, out_cs, N));
+  else
+    ZT_CUDA(launch_pdl(corr_lookup_kernel<float>, dim3(ceil_div(N, 4)), dim3(128), 0, (cudaStream_t)stream, a, coords, out, out_cs, N));
   return check_launch("corr_lookup_kernel");
+}
+
+extern "C" int zt_corr_lookup_f32(const float* l0, const float* l1, const float* l2, const float* l3,
+                                  const int* hs, const int* ws_, const float* coords, float* out, int out_cs,
+                                  int N, void* stream) {
+  return corr_lookup_any(l0, l1, l2, l3, false, hs, ws_, coords, out, out_cs, N, stream);
+}
+/* the same lookup over a bf16-storage pyramid (zt_corr_pyramid_bf16); interpolation and output stay fp32 */
+extern "C" int zt_corr_lookup_bf16(const void* l0, const void* l1, const void* l2, const void* l3,
+                                   const int* hs, const int* ws_, const float* coords, float* out, int out_cs,
+                                   int N, void* stream) {
+  return corr_lookup_any(l0, l1, l2, l3, true, hs, ws_, coords, out, out_cs, N, stream);
 }
 
 extern "C" int zt_convex_upsample_f32(const float* flow, int flow_cs, const float* mask, int mask_cs, float* out,

@@ -33,7 +33,7 @@ constexpr int CG_B_STAGE = 2 * 16384;                // Q stage: [hi rows 0..127
 constexpr int CG_NB = 3;
 
 struct CgArgs {
-  float* lvl[4];
+  void* lvl[4];          // fp32 or bf16 planes (template parameter of the kernel)
   int npos[4];           // h_l * w_l
   int tile0[5];          // first M tile of level l (tile0[4] = total M tiles)
   int N;                 // queries (= npos[0])
@@ -136,18 +136,22 @@ __device__ __forceinline__ void tmem_ld_wait2(uint32_t (&a)[16], uint32_t (&b)[1
                :: "memory");
 }
 // 16 queries x 32 positions: one coalesced 128 B warp store per query
-__device__ __forceinline__ void cg_store16(float* dst, int64_t npos, int nv, bool m_ok, float scale,
+__device__ __forceinline__ void cg_put(float* p, float v) { *p = v; }
+__device__ __forceinline__ void cg_put(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+template <typename OutT>
+__device__ __forceinline__ void cg_store16(OutT* dst, int64_t npos, int nv, bool m_ok, float scale,
                                            const uint32_t (&hi)[16], const uint32_t (&lo)[16]) {
   if (m_ok) {
 #pragma unroll
     for (int e = 0; e < 16; ++e)
-      if (e < nv) dst[(int64_t)e * npos] = (__uint_as_float(hi[e]) + __uint_as_float(lo[e])) * scale;
+      if (e < nv) cg_put(dst + (int64_t)e * npos, (__uint_as_float(hi[e]) + __uint_as_float(lo[e])) * scale);
   }
 }
 
 // Persistent: CTA b owns the flat work items [b*T/G, (b+1)*T/G) of the (M tile, query tile) grid, M tile major,
 // so the resident P tile changes at most a few times per CTA; it is reloaded k-block by k-block as the last
 // tile of the previous segment releases each k-block.
+template <typename OutT>
 __global__ void __launch_bounds__(CG_THREADS, 1) corr_gemm_kernel(const __grid_constant__ CUtensorMap tmPhi,
                                                                   const __grid_constant__ CUtensorMap tmPlo,
                                                                   const __grid_constant__ CUtensorMap tmQhi,
@@ -261,7 +265,7 @@ __global__ void __launch_bounds__(CG_THREADS, 1) corr_gemm_kernel(const __grid_c
     int cur_mt = -1;
     int64_t npos = 0;
     bool m_ok = false;
-    float* plane0 = nullptr;
+    OutT* plane0 = nullptr;
     for (int item = item0, lt = 0; item < item1; ++item, ++lt) {
       const int mt = item / a.q_tiles, j = item - mt * a.q_tiles;
       if (mt != cur_mt) {
@@ -270,7 +274,7 @@ __global__ void __launch_bounds__(CG_THREADS, 1) corr_gemm_kernel(const __grid_c
         // selects instead of dynamic indexing: keeps the kernel parameters out of local memory
         npos = l == 0 ? a.npos[0] : l == 1 ? a.npos[1] : l == 2 ? a.npos[2] : a.npos[3];
         const int t0l = l == 0 ? a.tile0[0] : l == 1 ? a.tile0[1] : l == 2 ? a.tile0[2] : a.tile0[3];
-        float* const lbase = l == 0 ? a.lvl[0] : l == 1 ? a.lvl[1] : l == 2 ? a.lvl[2] : a.lvl[3];
+        OutT* const lbase = reinterpret_cast<OutT*>(l == 0 ? a.lvl[0] : l == 1 ? a.lvl[1] : l == 2 ? a.lvl[2] : a.lvl[3]);
         const int m = (mt - t0l) * 128 + quad * 32 + lane;
         m_ok = m < npos;
         plane0 = lbase + (m_ok ? m : 0);
@@ -280,7 +284,7 @@ __global__ void __launch_bounds__(CG_THREADS, 1) corr_gemm_kernel(const __grid_c
       mbar_wait(accFull(buf), bph);
       tc_fence_after();
       const uint32_t t0 = tmem_base + lane_addr + buf * 256;
-      float* dst = plane0 + (int64_t)n0 * npos;
+      OutT* dst = plane0 + (int64_t)n0 * npos;
       const int nv = a.N - n0;                 // valid queries from n0 on (warp-uniform)
       uint32_t h0[16], l0[16], h1[16], l1[16];
       tmem_ld16_issue(t0, h0);
@@ -349,8 +353,8 @@ extern "C" int64_t zt_corr_pyramid_scratch_bytes(int h0, int w0) {
   return (int64_t)(2 * p.pk.Npad + 2 * p.pk.Ptot) * 256 * 2;
 }
 
-extern "C" int zt_corr_pyramid_f32(const float* fmap, int fm_rs, int h0, int w0, float* l0, float* l1, float* l2,
-                                   float* l3, void* scratch, int64_t scratch_bytes, void* stream) {
+static int corr_pyramid_any(const float* fmap, int fm_rs, int h0, int w0, void* l0, void* l1, void* l2, void* l3,
+                            bool out_bf16, void* scratch, int64_t scratch_bytes, void* stream) {
   using namespace zt;
   ZT_REQUIRE(fmap && l0 && l1 && l2 && l3 && scratch && h0 >= 8 && w0 >= 8 && fm_rs >= 256 && (fm_rs & 3) == 0,
              "corr_pyramid: bad args (grid %dx%d, row stride %d)", h0, w0, fm_rs);
@@ -389,10 +393,24 @@ extern "C" int zt_corr_pyramid_f32(const float* fmap, int fm_rs, int h0, int w0,
   const size_t smem = CG_BAR + CG_A_BYTES + CG_NB * CG_B_STAGE;
   static bool attr_done = false;
   if (!attr_done) {
-    ZT_CUDA(cudaFuncSetAttribute(corr_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ZT_CUDA(cudaFuncSetAttribute(corr_gemm_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ZT_CUDA(cudaFuncSetAttribute(corr_gemm_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_done = true;
   }
-  ZT_CUDA(launch_pdl(corr_gemm_kernel, dim3(grid), dim3(CG_THREADS), smem, st, tm[0], tm[1], tm[2], tm[3],
-                     a));
+  if (out_bf16)
+    ZT_CUDA(launch_pdl(corr_gemm_kernel<__nv_bfloat16>, dim3(grid), dim3(CG_THREADS), smem, st, tm[0], tm[1], tm[2], tm[3], a));
+  else
+    ZT_CUDA(launch_pdl(corr_gemm_kernel<float>, dim3(grid), dim3(CG_THREADS), smem, st, tm[0], tm[1], tm[2], tm[3], a));
   return check_launch("corr_gemm_kernel");
+}
+
+extern "C" int zt_corr_pyramid_f32(const float* fmap, int fm_rs, int h0, int w0, float* l0, float* l1, float* l2,
+                                   float* l3, void* scratch, int64_t scratch_bytes, void* stream) {
+  return corr_pyramid_any(fmap, fm_rs, h0, w0, l0, l1, l2, l3, false, scratch, scratch_bytes, stream);
+}
+/* bf16-storage variant (BASELINE.json configs[4] "fp32 vs bf16 corr"): same GEMM (fp32-grade products, fp32
+ * accumulation), the four levels are rounded to bf16 on the way out - half the bytes of the output-bound kernel */
+extern "C" int zt_corr_pyramid_bf16(const float* fmap, int fm_rs, int h0, int w0, void* l0, void* l1, void* l2,
+                                    void* l3, void* scratch, int64_t scratch_bytes, void* stream) {
+  return corr_pyramid_any(fmap, fm_rs, h0, w0, l0, l1, l2, l3, true, scratch, scratch_bytes, stream);
 }

@@ -54,8 +54,9 @@ def _param_version(module):
 # RAFT
 # ----------------------------------------------------------------------------------------
 def _tc_mode(name, default):
-    """Tensor-core mode of a sub-network: 3 = bf16 hi/lo split (fp32-grade), 1 = plain bf16,
-    0 = fp32 CUDA-core kernel.  Overridable for experiments with ZT_TC_<NAME>."""
+    """Tensor-core mode of a sub-network: 4 = scaled fp16 hi/lo split (three products, ~2^-22 per operand: fp32-grade),
+    3 = bf16 hi/lo split (three products, ~2^-17), 1 = plain bf16, 0 = fp32 CUDA-core kernel.  Overridable for
+    experiments with ZT_TC_<NAME>."""
     import os
     return int(os.environ.get("ZT_TC_" + name, default))
 
@@ -69,6 +70,9 @@ class RaftEngine:
     TC_HEAD = _tc_mode("RAFT_HEAD", TC)    # flow head + mask head
     TC_CORR = _tc_mode("RAFT_CORR", 3 if TC else 0)   # all-pairs correlation volume
     CORR_FUSED = int(os.environ.get("ZT_CORR_FUSED", "1"))   # volume + pyramid in one kernel (corr_gemm.cu)
+    # bf16 STORAGE of the correlation pyramid (configs[4] "fp32 vs bf16 corr"): halves the bytes of the output-bound
+    # pyramid kernel; off by default - its EPE against the reference is reported beside the fp32 arm
+    CORR_BF16 = int(os.environ.get("ZT_CORR_BF16", "0"))
     BN96 = int(os.environ.get("ZT_ENC_BN96", "1"))
     # N tiles of the two K = 2304 layers of the motion encoder (measured: 48 / 32 instead of 64 put 120 instead of
     # 90 / 60 CTAs on the K loop and change the iteration time by < 1 %: these launches are not K-loop bound)
@@ -78,6 +82,11 @@ class RaftEngine:
     BN_Q = int(os.environ.get("ZT_BN_Q", "64"))        # GRU q conv (N = 128)
     BN_C1 = int(os.environ.get("ZT_BN_C1", "128"))      # motion encoder convc1 (N = 256)
     BN_FH = int(os.environ.get("ZT_BN_FH", "128"))      # flow head conv1 (N = 256)
+    # all update iterations in one persistent cooperative kernel (csrc/raft_update.cu); 0 = the round-1 launch chain
+    UPD_FUSED = int(os.environ.get("ZT_RAFT_FUSED", "1"))
+    # N tiles of the nine tensor-core layers inside that kernel (convc1, convf2, convc2, conv, zr1, q1, zr2, q2, fh1)
+    FUSED_BN = tuple(int(v) for v in os.environ.get("ZT_RAFT_FUSED_BN", "64,64,64,32,64,32,64,32,64").split(","))
+    FUSED_MAX_CTAS = int(os.environ.get("ZT_RAFT_FUSED_CTAS", "0"))
 
     def __init__(self, raft):
         self.raft = raft
@@ -274,12 +283,15 @@ class RaftEngine:
                 ev = torch.cuda.Event()
                 ev.record(side)
                 cur.wait_event(ev)
+        fused = bool(self.UPD_FUSED) and self.TC_UPD in (3, 4) and self.TC_HEAD == self.TC_UPD
         hx = ws.get("hx", (N, 384))
+        # fused update kernel: the hidden state is its own dense tensor (fp32 master; the kernel keeps bf16 hi/lo copies)
+        hbuf, hcs = (ws.get("h128", (N, 128)), 128) if fused else (hx, 384)
         gru_pre = {}
         fork()
         with torch.cuda.stream(side):
             c, ch, cwid = self._encoder("cnet", x2, 1, hp, wp, True)
-            ops.conv2d(w["cnet.conv2.net"], c, 128, 128, 1, h8, w8, hx, 384, act="tanh", tc=T, bn=64)
+            ops.conv2d(w["cnet.conv2.net"], c, 128, 128, 1, h8, w8, hbuf, hcs, act="tanh", tc=T, bn=64)
             ops.conv2d(w["cnet.conv2.inp"], c, 128, 128, 1, h8, w8, hx, 384, out_off=128, act="relu", tc=T, bn=64)
             if self.TC_UPD:
                 for s_, pad_ in (("1", (0, 2)), ("2", (2, 0))):
@@ -301,7 +313,8 @@ class RaftEngine:
         if hs[3] < 2 or wsz[3] < 2:
             raise RuntimeError("RAFT grid %dx%d is too small: the reference's 4-level lookup yields NaN when the "
                                "coarsest level is below 2x2 (needs a feature grid >= 16x16)" % (h8, w8))
-        lv = [ws.get(f"corr{i}", (N, hs[i] * wsz[i])) for i in range(4)]
+        corr_dt = torch.bfloat16 if (self.CORR_BF16 and self.TC_CORR and self.CORR_FUSED) else torch.float32
+        lv = [ws.get(f"corr{i}", (N, hs[i] * wsz[i]), corr_dt) for i in range(4)]
         if self.TC_CORR and self.CORR_FUSED:
             # volume + all three pooled levels from one tcgen05 accumulator (corr_gemm.cu)
             scratch = ws.get("corr_scratch", (ops.corr_pyramid_scratch_bytes(h8, w8) // 4,))
@@ -333,8 +346,10 @@ class RaftEngine:
             grid = torch.stack([xs, ys], -1).float().reshape(N, 2).contiguous()
             ws.bufs[("grid", h8, w8)] = grid
         coords1 = ws.get("coords1", (N, 2))
-        coords1.copy_(grid)
         flow4 = ws.get("flow4", (N, 4), zero=True)
+        if fused:
+            return self._finish_fused(w, ws, lv, hs, wsz, hbuf, gru_pre, coords1, flow4, fmap, h8, w8, hp, wp, iters, join)
+        coords1.copy_(grid)
         corr = ws.get("corrfeat", (N, 324))
         c1 = ws.get("c1", (N, 256))
         c2f = ws.get("c2f", (N, 256))
@@ -389,6 +404,32 @@ class RaftEngine:
         flow_up = ws.get("flow_up", (1, 2, hp, wp))
         ops.convex_upsample(flow4, 4, mask, 576, flow_up, h8, w8)
         self.last = dict(fmap=fmap, levels=lv, hs=hs, ws=wsz, flow4=flow4, hx=hx, corr=corr, N=N, h8=h8, w8=w8)
+        return flow_up
+
+    def _finish_fused(self, w, ws, lv, hs, wsz, h, gru_pre, coords1, flow4, fmap, h8, w8, hp, wp, iters, join):
+        """The update loop (raft.py:111-120) as ONE persistent kernel, then mask head + convex upsampling of the last
+        prediction.  Activations between the layers live as bf16 hi/lo pairs (TMA-fed tensor cores)."""
+        N, bf = h8 * w8, torch.bfloat16
+        bufs = dict(h=h, coords1=coords1, flow4=flow4, z=ws.get("z", (N, 128)), fhid=ws.get("fhid", (N, 256)),
+                    counter=ws.get("ru.counter", (4,), torch.int32, zero=True))
+        for name, cn in (("corr", 384), ("c1", 256), ("f1", 128), ("c2f", 256), ("hm", 256), ("rh", 128)):
+            for sfx in ("_hi", "_lo"):
+                # corr: channels 324..383 are never written and must read as zero (K padding of convc1)
+                bufs[name + sfx] = ws.get("ru." + name + sfx, (N, cn), bf, zero=True)
+        wl = [w["enc.convc1"], w["enc.convf2"], w["enc.convc2"], w["enc.conv"], w["gru.zr1.hm"], w["gru.q1.hm"],
+              w["gru.zr2.hm"], w["gru.q2.hm"], w["fh1"]]
+        join()   # context network, hidden state and GRU planes are ready
+        ops.raft_update(h8, w8, iters, bufs, (gru_pre["zr1"], gru_pre["q1"], gru_pre["zr2"], gru_pre["q2"]), lv, hs, wsz,
+                        wl, self.FUSED_BN, w["enc.convf1.raw"][0], w["enc.convf1.raw"][1], w["fh2.raw"][0], w["fh2.raw"][1],
+                        max_ctas=self.FUSED_MAX_CTAS, fp16=(self.TC_UPD == 4))
+        TH = self.TC_HEAD
+        mh = ws.get("maskh", (N, 256))
+        mask = ws.get("mask", (N, 576))
+        ops.conv2d(w["mask0"], h, 128, 128, 1, h8, w8, mh, 256, pad=(1, 1), act="relu", tc=TH, bn=64)
+        ops.conv2d(w["mask2"], mh, 256, 256, 1, h8, w8, mask, 576, scale=0.25, tc=TH, bn=64)
+        flow_up = ws.get("flow_up", (1, 2, hp, wp))
+        ops.convex_upsample(flow4, 4, mask, 576, flow_up, h8, w8)
+        self.last = dict(fmap=fmap, levels=lv, hs=hs, ws=wsz, flow4=flow4, hx=None, corr=None, N=N, h8=h8, w8=w8, h=h)
         return flow_up
 
     def forward(self, image1, image2, iters=12):

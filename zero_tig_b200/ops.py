@@ -5,12 +5,14 @@ CUDA stream; outputs are caller- or torch-allocated.  No wrapper has a CPU path:
 non-CUDA tensor raises.
 """
 import ctypes as C
+import math
 
 import torch
 
 from . import _lib
-from ._lib import ZtConv, ZtConvBf16, check, lib
+from ._lib import ZtConv, ZtConvBf16, ZtRaftUpdate, check, lib
 
+F16_ACT_SCALE = 16.0      # ZT_F16_ACT_SCALE of include/zerotig.h (split mode 4)
 ACT = {"none": 0, "relu": 1, "lrelu": 2, "sigmoid": 3, "tanh": 4}
 EPI = {"plain": 0, "gru_zr": 1, "gru_q": 2, "add_relu": 3, "add": 4}
 
@@ -30,7 +32,7 @@ def _p(t, offset_elems=0):
 
 class ConvW:
     """A conv layer's parameters in kernel layout: weight [kh][kw][cin_pad][w_cs], bias [cout]."""
-    __slots__ = ("w", "b", "kh", "kw", "cin", "cout", "w_cs", "w_raw", "b_raw", "_tc")
+    __slots__ = ("w", "b", "kh", "kw", "cin", "cout", "w_cs", "w_raw", "b_raw", "_tc", "w_scale")
 
     def __init__(self, weight, bias=None, cin_pad=None, bn=None, eps=1e-5, out_slice=None):
         w = weight.detach().float()
@@ -53,23 +55,41 @@ class ConvW:
         self.kh, self.kw, self.cin, self.cout, self.w_cs = kh, kw, cin_p, cout, w_cs
         self.w_raw, self._tc = w, {}
         self.b_raw = b
+        self.w_scale = None      # power of two applied to the weights of the scaled-fp16 packing (split mode 4)
 
-    def tc_pack(self, BN):
-        """bf16 hi/lo weights in the tcgen05 kernel's layout (csrc/conv_tc.cu):
+    def f16_scale(self):
+        """Power of two that brings max|w| into (4096, 8192] (split mode 4): the fp16 low halves of the scaled weights
+        stay normal numbers (>= 2^-14), so hi + lo carries ~22 bits.  Computed once per ConvW (one host sync)."""
+        if self.w_scale is None:
+            m = float(self.w_raw.abs().max())
+            e = 13 - math.frexp(m)[1] if m > 0 else 10        # m = f * 2^e', f in [0.5, 1): m * 2^(13 - e') in [4096, 8192)
+            self.w_scale = float(2.0 ** max(min(e, 24), -8))
+        return self.w_scale
+
+    def acc_scale(self):
+        """ZtConv.acc_scale of split mode 4: undoes the activation and weight scales on the fp32 accumulator."""
+        return 1.0 / (F16_ACT_SCALE * self.f16_scale())
+
+    def tc_pack(self, BN, fp16=False):
+        """hi/lo weights in the tcgen05 kernel's layout (csrc/conv_tc.cu):
         [n_tile][64-channel group][tap][hi|lo][row BN][128 B], each 128 B row (64 input channels
         of one tap) stored with the UMMA 128-byte swizzle (16 B chunk c of row n at chunk
         position c ^ (n & 7)) - one contiguous block per (n_tile, group, tap) = one
-        cp.async.bulk per weight stage."""
-        t = self._tc.get(BN)
+        cp.async.bulk per weight stage.  bf16 pairs of w (split modes 1, 3) or fp16 pairs of w * f16_scale() (mode 4)."""
+        key = (BN, "f16") if fp16 else BN
+        t = self._tc.get(key)
         if t is None:
             w = self.w_raw
             cout, cin, kh, kw = w.shape
             ng, nt = (self.cin + 63) // 64, (cout + BN - 1) // BN
             wp = torch.zeros(nt * BN, ng * 64, kh, kw, device=w.device, dtype=torch.float32)
             wp[:cout, :cin] = w
-            hi = wp.to(torch.bfloat16)
-            lo = (wp - hi.float()).to(torch.bfloat16)
-            x = torch.stack([hi, lo], 0).reshape(2, nt, BN, ng, 8, 8, kh * kw)
+            dt = torch.float16 if fp16 else torch.bfloat16
+            if fp16:
+                wp = wp * self.f16_scale()
+            hi = wp.to(dt)
+            lo = (wp - hi.float()).to(dt)
+            x = torch.stack([hi, lo], 0).view(torch.int16).reshape(2, nt, BN, ng, 8, 8, kh * kw)
             x = x.permute(1, 3, 6, 0, 2, 4, 5).contiguous()      # nt, g, tap, part, row, chunk, e
             n = torch.arange(BN, device=w.device)
             src = torch.arange(8, device=w.device)[None, :] ^ (n[:, None] & 7)   # position j <- chunk j^(n&7)
@@ -78,7 +98,7 @@ class ConvW:
             # constant weights are fetched BEFORE griddepcontrol.wait by the kernel (programmatic dependent
             # launch): make sure the one-time packing has really finished before the first launch
             torch.cuda.current_stream().synchronize()
-            self._tc[BN] = t
+            self._tc[key] = t
         return t
 
 
@@ -169,9 +189,14 @@ def conv2d(wt: ConvW, in0, in0_cs, c0, B, H, W, out, out_cs, *, in0_off=0, in1=N
     d.aux1, d.aux1_cs = _p(aux1, aux1_off), aux1_cs
     d.bplane, d.bplane_cs = _p(bplane), bplane_cs
     if tc:
-        # tensor-core path: tc = 1 (bf16) or 3 (bf16 hi/lo split, 3 products ~ fp32-grade)
+        # tensor-core path: tc = 1 (bf16), 3 (bf16 hi/lo split, 3 products) or 4 (scaled fp16 hi/lo split, 3 products:
+        # fp32-grade)
         BN = bn or min((wt.cout + 15) // 16 * 16, 128)
-        d.weight = _p(wt.tc_pack(BN))
+        if tc == 4:
+            d.weight = _p(wt.tc_pack(BN, fp16=True))
+            d.acc_scale = wt.acc_scale()
+        else:
+            d.weight = _p(wt.tc_pack(BN))
         # bit 8: weights written by the preceding kernel (RowsAsWeights) - see the PDL note in csrc/conv_tc.cu
         check(lib().zt_conv2d_tc_nhwc(C.byref(d), BN, tc | (0x100 if isinstance(wt, RowsAsWeights) else 0), _stream()),
               "conv2d_tc")
@@ -235,6 +260,39 @@ def flow_head2_update(x, x_cs, Cn, w, b, coords1, f1, f1_cs, f2, f2_cs, f2_off, 
                                          H, W, _stream()), "flow_head2_update")
 
 
+RAFT_UPDATE_LAYERS = ("convc1", "convf2", "convc2", "conv", "zr1", "q1", "zr2", "q2", "fh1")
+
+
+def raft_update(h8, w8, iters, bufs, bplanes, levels, hs, ws, weights, bns, wf1, bf1, wfh2, bfh2, max_ctas=0, fp16=False):
+    """All `iters` iterations of the RAFT update block in one persistent cooperative kernel (csrc/raft_update.cu;
+    raft.py:111-120).  bufs: dict of the device buffers named in ZtRaftUpdate (corr_hi .. rh_lo bf16, h / z / fhid /
+    coords1 / flow4 fp32, counter int32); bplanes: (zr1, q1, zr2, q2); weights: ConvW per RAFT_UPDATE_LAYERS entry,
+    bns: their N tiles."""
+    d = ZtRaftUpdate()
+    d.h8, d.w8, d.iters, d.max_ctas = h8, w8, iters, max_ctas
+    for n in ("corr", "c1", "f1", "c2f", "hm", "rh"):
+        for sfx in ("_hi", "_lo"):
+            setattr(d, n + sfx, _p(bufs[n + sfx]))
+    for n in ("h", "z", "fhid", "coords1", "flow4", "counter"):
+        setattr(d, n, _p(bufs[n]))
+    d.bp_zr1, d.bp_q1, d.bp_zr2, d.bp_q2 = [_p(t) for t in bplanes]
+    for i in range(4):
+        d.lvl[i], d.lh[i], d.lw[i] = levels[i].data_ptr(), hs[i], ws[i]
+    d.lvl_bf16 = int(levels[0].dtype == torch.bfloat16)
+    d.fp16 = int(fp16)
+    for i, (wt, bn) in enumerate(zip(weights, bns)):
+        d.w[i] = wt.tc_pack(bn, fp16=fp16).data_ptr()
+        d.b[i] = wt.b.data_ptr() if wt.b is not None else None
+        d.bn[i] = bn
+        d.acc_scale[i] = wt.acc_scale() if fp16 else 1.0
+    d.wf1, d.bf1, d.wfh2, d.bfh2 = _p(wf1), _p(bf1), _p(wfh2), _p(bfh2)
+    check(lib().zt_raft_update(C.byref(d), _stream()), "raft_update")
+
+
+def split_bf16_hilo(x, rs, hi, lo, out_rs, Cn, N):
+    check(lib().zt_split_bf16_hilo(_p(x), rs, _p(hi), _p(lo), out_rs, Cn, N, _stream()), "split_bf16_hilo")
+
+
 def instnorm(x, x_cs, out, out_cs, stats, B, HW, Cn, relu_inner, relu_outer=False, res=None, res_cs=0, eps=1e-5):
     check(lib().zt_instnorm_nhwc_f32(_p(x), x_cs, _p(out), out_cs, _p(res), res_cs, _p(stats), B, HW, Cn,
                                      eps, int(relu_inner), int(relu_outer), _stream()), "instnorm")
@@ -253,16 +311,19 @@ def corr_pyramid_scratch_bytes(h0, w0):
 
 
 def corr_pyramid(fmap, fm_rs, h0, w0, levels, scratch):
-    """All-pairs correlation + 4-level pyramid in one tcgen05 kernel (corr.py:13-27,52-60)."""
-    check(lib().zt_corr_pyramid_f32(_p(fmap), fm_rs, h0, w0, _p(levels[0]), _p(levels[1]), _p(levels[2]),
+    """All-pairs correlation + 4-level pyramid in one tcgen05 kernel (corr.py:13-27,52-60).  The storage type of
+    `levels` (fp32 or bf16) selects the entry point."""
+    fn = lib().zt_corr_pyramid_bf16 if levels[0].dtype == torch.bfloat16 else lib().zt_corr_pyramid_f32
+    check(fn(_p(fmap), fm_rs, h0, w0, _p(levels[0]), _p(levels[1]), _p(levels[2]),
                                     _p(levels[3]), _p(scratch), scratch.numel() * scratch.element_size(), _stream()),
           "corr_pyramid")
 
 
 def corr_lookup(levels, hs, ws, coords, out, out_cs, N):
     IA = C.c_int * 4
-    check(lib().zt_corr_lookup_f32(_p(levels[0]), _p(levels[1]), _p(levels[2]), _p(levels[3]),
-                                   IA(*hs), IA(*ws), _p(coords), _p(out), out_cs, N, _stream()), "corr_lookup")
+    fn = lib().zt_corr_lookup_bf16 if levels[0].dtype == torch.bfloat16 else lib().zt_corr_lookup_f32
+    check(fn(_p(levels[0]), _p(levels[1]), _p(levels[2]), _p(levels[3]),
+             IA(*hs), IA(*ws), _p(coords), _p(out), out_cs, N, _stream()), "corr_lookup")
 
 
 def convex_upsample(flow, flow_cs, mask, mask_cs, out, h8, w8):

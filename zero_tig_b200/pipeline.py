@@ -105,6 +105,17 @@ class FramePipeline:
             emit(i, *self.host_out[slot])
 
 
+def share_sms(models):
+    """Throughput mode for S model replicas on one GPU: the persistent RAFT update kernel (csrc/raft_update.cu) is a
+    cooperative launch that would otherwise claim all 148 SMs, so the chains of different shards could not overlap
+    inside it; each replica's kernel is limited to 148 // S CTAs (measured at 1080p: 3 shards x 49 CTAs 248 frames/s,
+    3 x 148 222 frames/s; a lone sequence runs fastest on the full grid).  A single replica keeps the full grid."""
+    n = len(models)
+    for m in models:
+        eng = m.raft.engine()
+        eng.FUSED_MAX_CTAS = 0 if n <= 1 else max(30, 148 // n)
+
+
 class MultiShardPipeline:
     """Several frame-range shards of a clip on ONE GPU (the same unit ``shard.plan`` deals to the GPUs of a box: a
     contiguous frame range preceded by one halo frame), each with its own model replica, recurrent state,
@@ -121,6 +132,7 @@ class MultiShardPipeline:
             raise ValueError("MultiShardPipeline needs at least one model replica")
         self.pipes = [FramePipeline(m, H, W, depth=depth, quantize_u8=quantize_u8, input_u8=input_u8, graph=graph)
                       for m in models]
+        share_sms(models)
         self.dev = self.pipes[0].dev
         self.streams = [torch.cuda.Stream(self.dev) for _ in models]
         self.h2d_bytes, self.d2h_bytes = self.pipes[0].h2d_bytes, self.pipes[0].d2h_bytes
