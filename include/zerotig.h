@@ -88,6 +88,15 @@ int zt_conv2d_nhwc_f32(const ZtConv* d, void* stream);
 #define ZT_F16_ACT_SCALE 16.0f
 int zt_conv2d_tc_nhwc(const ZtConv* d, int BN, int split, void* stream);
 
+/* nn.Conv2d weights [cout][cin][kh][kw] fp32 (the live parameter, train.py:98) -> the packed weight operand of
+ * zt_conv2d_tc_nhwc, on the device (no host tensor ops, no synchronisation): bf16 hi/lo pairs, or (fp16 != 0) fp16
+ * pairs of weight * scale (split mode 4).  dgrad != 0 packs the weights of the DATA-GRADIENT convolution instead
+ * (in/out channels swapped, taps mirrored: dX = conv(dY, W')).  cin_pad: padded K channel count (0 = round up to 4).
+ * out: ceil(rows/BN)*BN * ceil(cin_pad/64)*64 * kh*kw * 4 bytes.  Launch the convolution with split | 0x100 (weights
+ * written by the preceding kernel). */
+int zt_pack_tc_weights_f32(const float* w, int cout, int cin, int kh, int kw, int cin_pad, int dgrad, int BN, int fp16,
+                           float scale, void* out, void* stream);
+
 /* Pack R rows x C fp32 (row stride rs) as the weight operand of zt_conv2d_tc_nhwc for a 1x1
  * convolution with cout = R whose weights are produced on the device every frame: the all-pairs
  * correlation corr.py:52-60 (weights = fmap2).  out: ceil(R/BN)*BN * ceil(C/64)*64 * 4 bytes. */

@@ -67,6 +67,7 @@ SIGNATURES = {
     "zt_debug_set_raft_update_trace": [P, I],
     "zt_split_bf16_hilo": [P, I, P, P, I, I, L, P],
     "zt_pack_tc_rows_f32": [P, I, I, I, I, P, P],
+    "zt_pack_tc_weights_f32": [P, I, I, I, I, I, I, I, I, F, P, P],
     "zt_instnorm_nhwc_f32": [P, I, P, I, P, I, P, I, I, I, F, I, I, P],
     "zt_transpose_f32": [P, I, I, I, P, I, P],
     "zt_avgpool2_f32": [P, P, L, I, I, P],

@@ -628,6 +628,60 @@ __global__ void pack_tc_rows_kernel(const float* __restrict__ rows, int R, int C
 }
 }  // namespace zt
 
+namespace zt {
+// nn.Conv2d weights [cout][cin][kh][kw] fp32 (live parameter storage) -> the hi/lo operand layout of conv_tc_kernel
+// [n_tile][64-ch group][tap][hi|lo][row BN][128 B swizzled], on the device: the zero-shot training loop changes the
+// weights every step, and re-packing them with host tensor ops cost ~20 small launches and a stream synchronise
+// per layer.  element(n, c, tap) = w[n * sn + c * sc + tap'] with tap' = tap, or the mirrored tap when `flip`
+// (data-gradient convolution: in/out channels swapped through sn / sc, taps mirrored).
+__global__ void pack_tc_weights_kernel(const float* __restrict__ w, int N, int Cin, int ntaps, int sn, int sc, int flip,
+                                       int BN, int ngroups, int fp16, float scale, uint8_t* __restrict__ out, int64_t total) {
+  pdl_enter();
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int chunk = (int)(i & 7);
+    int64_t r = i >> 3;
+    const int row = (int)(r % BN); r /= BN;
+    const int tap = (int)(r % ntaps); r /= ntaps;
+    const int g = (int)(r % ngroups);
+    const int nt = (int)(r / ngroups);
+    const int n = nt * BN + row;
+    const int st = flip ? ntaps - 1 - tap : tap;
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int c = g * 64 + chunk * 8 + e;
+      v[e] = (n < N && c < Cin) ? __ldg(w + (int64_t)n * sn + (int64_t)c * sc + st) * scale : 0.f;
+    }
+    uint2 h0, l0, h1, l1;
+    if (fp16) { split4h(make_float4(v[0], v[1], v[2], v[3]), h0, l0); split4h(make_float4(v[4], v[5], v[6], v[7]), h1, l1); }
+    else { split4(make_float4(v[0], v[1], v[2], v[3]), h0, l0); split4(make_float4(v[4], v[5], v[6], v[7]), h1, l1); }
+    const size_t part = (size_t)BN * 128;
+    uint8_t* dst = out + ((size_t)((nt * ngroups + g) * ntaps + tap) * 2) * part + (size_t)row * 128 + ((size_t)(chunk ^ (row & 7)) << 4);
+    *reinterpret_cast<uint4*>(dst) = make_uint4(h0.x, h0.y, h1.x, h1.y);
+    *reinterpret_cast<uint4*>(dst + part) = make_uint4(l0.x, l0.y, l1.x, l1.y);
+  }
+}
+}  // namespace zt
+
+extern "C" int zt_pack_tc_weights_f32(const float* w, int cout, int cin, int kh, int kw, int cin_pad, int dgrad, int BN,
+                                      int fp16, float scale, void* out, void* stream) {
+  using namespace zt;
+  ZT_REQUIRE(w && out && cout > 0 && cin > 0 && kh >= 1 && kw >= 1 && kh <= 7 && kw <= 7, "pack_tc_weights: bad args");
+  ZT_REQUIRE(BN >= 16 && BN <= 256 && (BN & 15) == 0 && ((uintptr_t)out & 15) == 0, "pack_tc_weights: bad BN %d / alignment", BN);
+  ZT_REQUIRE(scale > 0.f, "pack_tc_weights: scale must be positive");
+  // forward: rows = cout, K channels = cin; data gradient: rows = cin, K channels = cout, taps mirrored
+  const int N = dgrad ? cin : cout, C = dgrad ? cout : cin, taps = kh * kw;
+  const int sn = dgrad ? taps : cin * taps, sc = dgrad ? cin * taps : taps;
+  const int cp = cin_pad > 0 ? cin_pad : (C + 3) / 4 * 4;
+  ZT_REQUIRE(cp >= C, "pack_tc_weights: cin_pad %d < %d", cp, C);
+  const int ngroups = ceil_div(cp, TC_CG), nt = ceil_div(N, BN);
+  const int64_t total = (int64_t)nt * ngroups * taps * BN * 8;
+  const int blocks = (int)std::min<int64_t>(ceil_div64(total, 256), 4 * kNumSMs);
+  ZT_CUDA(launch_pdl(pack_tc_weights_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, w, N, C, taps, sn, sc, dgrad ? 1 : 0,
+                     BN, ngroups, fp16 ? 1 : 0, scale, (uint8_t*)out, total));
+  return check_launch("pack_tc_weights_kernel");
+}
+
 extern "C" int zt_pack_tc_rows_f32(const float* rows, int R, int C, int rs, int BN, void* out, void* stream) {
   using namespace zt;
   ZT_REQUIRE(rows && out && R > 0 && C > 0 && (C & 7) == 0 && (rs & 3) == 0 && rs >= C, "pack_tc_rows: bad args");
@@ -663,7 +717,7 @@ extern "C" int zt_conv2d_tc_nhwc(const ZtConv* dp, int BN, int split, void* stre
              "conv_tc: split must be 1 (bf16), 3 (bf16 hi/lo, 3 products) or 4 (scaled fp16 hi/lo, 3 products); got %d", split);
   const bool fp16 = split == 4;
   if (fp16) split = 3;
-  ZT_REQUIRE(!fp16 || (d.acc_scale > 0.f && !w_dynamic), "conv_tc: split 4 needs acc_scale = 1 / (activation scale * weight scale) and host-packed weights");
+  ZT_REQUIRE(!fp16 || d.acc_scale > 0.f, "conv_tc: split 4 needs acc_scale = 1 / (activation scale * weight scale)");
   ZT_REQUIRE(BN >= 16 && BN <= 256 && (BN & 15) == 0, "conv_tc: BN=%d must be a multiple of 16 in [16,256]", BN);
   ZT_REQUIRE(d.sh == 1 && d.sw == 1, "conv_tc: stride-1 convolutions only (got %dx%d)", d.sh, d.sw);
   ZT_REQUIRE((d.c0 & 3) == 0 && (d.c1 & 3) == 0 && cin > 0, "conv_tc: channel counts must be multiples of 4 (c0=%d c1=%d)", d.c0, d.c1);

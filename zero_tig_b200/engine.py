@@ -707,15 +707,68 @@ class TrainEngine(FrameEngine):
     TC_D2 = _tc_mode("TRAIN_D2", 3)
     TC_BWD = _tc_mode("TRAIN_BWD", 3)
 
+    # weights of the tensor-core paths are re-packed by a device kernel after every optimiser step (ops.DevConvW)
+    DEV_PACK = int(os.environ.get("ZT_TRAIN_DEVPACK", "1"))
+
+    def _dev_pack_ok(self, device):
+        m = self.model
+        return (self.DEV_PACK and all(t in (3, 4) for t in (self.TC_D1, self.TC_ENH, self.TC_D2, self.TC_BWD)) and
+                all(p.device == device and p.dtype == torch.float32 and p.is_contiguous()
+                    for mod in (m.enhance, m.denoise_1, m.denoise_2) for p in mod.parameters()))
+
     def _prepare(self, device):
         m = self.model
         key = (str(device), _param_version(m.enhance), _param_version(m.denoise_1), _param_version(m.denoise_2))
+        if self._dev_pack_ok(device):
+            ptrs = tuple(p.data_ptr() for mod in (m.enhance, m.denoise_1, m.denoise_2) for p in mod.parameters())
+            if getattr(self, "_devw_ptrs", None) != ptrs:        # first use (or the parameters moved): build the packers
+                from .ops import DevConvW
+                e, w, wb = m.enhance, {}, {}
+                for n, d, cp in (("d1", m.denoise_1, 4), ("d2", m.denoise_2, 12)):
+                    w[n + ".c1"] = DevConvW(d.conv1.weight, d.conv1.bias, cin_pad=cp)
+                    w[n + ".c2"] = DevConvW(d.conv2.weight, d.conv2.bias)
+                    w[n + ".c3"] = DevConvW(d.conv3.weight, d.conv3.bias)
+                w["e.in"] = DevConvW(e.in_conv[0].weight, e.in_conv[0].bias, cin_pad=12)
+                w["e.blk_raw"] = DevConvW(e.conv[0].weight, e.conv[0].bias)
+                w["e.out"] = DevConvW(e.out_conv[0].weight, e.out_conv[0].bias)
+                wb["e.out"] = DevConvW(e.out_conv[0].weight, None, cin_pad=4, dgrad=True)
+                wb["e.blk"] = DevConvW(e.conv[0].weight, None, dgrad=True)
+                wb["d1.c3"] = DevConvW(m.denoise_1.conv3.weight, None, cin_pad=4, dgrad=True)
+                wb["d1.c2"] = DevConvW(m.denoise_1.conv2.weight, None, dgrad=True)
+                wb["d2.c3"] = DevConvW(m.denoise_2.conv3.weight, None, cin_pad=8, dgrad=True)
+                wb["d2.c2"] = DevConvW(m.denoise_2.conv2.weight, None, dgrad=True)
+                wb["d2.c1"] = DevConvW(m.denoise_2.conv1.weight, None, dgrad=True)
+                self.w, self._wbwd, self._devw_ptrs, self._wkey, self._wg = w, wb, ptrs, key, None
+                self._eval_key = None
+                if self.ws is None or self.ws.device != device:
+                    self.ws = _Workspace(device)
+            elif key != self._wkey:                              # an optimiser step happened: one small kernel per layer
+                for d_ in (self.w, self._wbwd):
+                    for wt in d_.values():
+                        if getattr(wt, "dynamic", False):
+                            wt.repack()
+                self._wkey = key
+            return
+        self._devw_ptrs = None
         fresh = key != self._wkey
         super()._prepare(device)
         if fresh:   # train-mode BatchNorm needs the un-folded block convolution
             e = m.enhance
             self.w["e.blk_raw"] = ConvW(e.conv[0].weight.to(device), e.conv[0].bias.to(device))
             self._wbwd = None
+
+    def _eval_block(self, device):
+        """Eval-mode forward of the training model (train.py:138): the BatchNorm-folded block convolution is packed on
+        the host (rare: once per evaluation pass)."""
+        if getattr(self, "_devw_ptrs", None) is None:
+            return
+        if getattr(self, "_eval_key", None) != self._wkey:
+            e = self.model.enhance
+            bnm = e.conv[1]
+            self.w["e.blk"] = ConvW(e.conv[0].weight.to(device), e.conv[0].bias.to(device),
+                                    bn=(bnm.weight.to(device), bnm.bias.to(device), bnm.running_mean.to(device),
+                                        bnm.running_var.to(device)), eps=bnm.eps)
+            self._eval_key = self._wkey
 
     # L_pred = x - denoise_1(x) without clamp (model.py:149-150)
     def denoise1_residual(self, x, H, W, tag=""):
@@ -776,6 +829,7 @@ class TrainEngine(FrameEngine):
         if training:
             s2, H2 = self.enhance_train(x, H3_wp, s3_wp, L2, H, W)
         else:
+            self._eval_block(x.device)
             s2, H2 = self.enhance_H2(x, H3_wp, s3_wp, L2, H, W)
         s21, s22 = ops.pair_downsample(s2)
         H11 = ops.div_clamp(L11, 0.0, s21, eps, 1.0)
@@ -839,6 +893,10 @@ class TrainEngine(FrameEngine):
 
     # ---- backward (train.py:129 loss.backward()) ----
     def _prepare_bwd(self, device):
+        if getattr(self, "_devw_ptrs", None) is not None:      # device-packed data-gradient weights exist already
+            if getattr(self, "_wg", None) is None:
+                self._make_wgrads(device)
+            return
         if getattr(self, "_wbwd", None) is not None:
             return
         m, w = self.model, {}
@@ -852,6 +910,12 @@ class TrainEngine(FrameEngine):
         w["d2.c1"] = ops.dgrad_weights(d2.conv1.weight.to(device))
         self._wbwd = w
         if getattr(self, "_wg", None) is None:
+            self._make_wgrads(device)
+
+    def _make_wgrads(self, device):
+        m = self.model
+        e, d1, d2 = m.enhance, m.denoise_1, m.denoise_2
+        if True:
             fw = self.w
             self._wg = {
                 "e.in": ops.WGrad(fw["e.in"], e.in_conv[0].weight.shape, device),

@@ -198,16 +198,64 @@ def conv2d(wt: ConvW, in0, in0_cs, c0, B, H, W, out, out_cs, *, in0_off=0, in1=N
         else:
             d.weight = _p(wt.tc_pack(BN))
         # bit 8: weights written by the preceding kernel (RowsAsWeights) - see the PDL note in csrc/conv_tc.cu
-        check(lib().zt_conv2d_tc_nhwc(C.byref(d), BN, tc | (0x100 if isinstance(wt, RowsAsWeights) else 0), _stream()),
+        check(lib().zt_conv2d_tc_nhwc(C.byref(d), BN, tc | (0x100 if getattr(wt, "dynamic", False) else 0), _stream()),
               "conv2d_tc")
     else:
         check(lib().zt_conv2d_nhwc_f32(C.byref(d), _stream()), "conv2d")
     return Ho, Wo
 
 
+class DevConvW:
+    """Conv weights that are (re)packed ON THE DEVICE from the live nn.Parameter (zt_pack_tc_weights_f32): the
+    zero-shot training loop (train.py:126-131) changes the weights every step, and packing them with host tensor ops
+    cost ~20 small launches plus a stream synchronise per layer and step.  ``repack()`` after every optimiser step; the
+    convolution is launched with the dynamic-weights flag so it waits for the packer.  dgrad=True packs the weights of
+    the data-gradient convolution (channels swapped, taps mirrored).  Tensor-core modes only (3 = bf16 pairs, 4 =
+    scaled fp16 pairs with a fixed weight scale: trainable weights start at N(0, 0.02) and stay far below 64)."""
+    dynamic = True
+    F16_W_SCALE = 1024.0
+
+    def __init__(self, weight, bias=None, cin_pad=None, dgrad=False):
+        self.weight, self.b, self.dgrad = weight, bias, dgrad
+        co, ci, self.kh, self.kw = weight.shape
+        self.cout, cin = (ci, co) if dgrad else (co, ci)
+        self.cin = cin_pad or ((cin + 3) // 4 * 4)
+        self.w_cs = (self.cout + 3) // 4 * 4
+        self.w, self.w_scale, self._bufs = None, None, {}
+        self.w_raw = weight.detach().transpose(0, 1) if dgrad else weight.detach()     # shape bookkeeping (bench, WGrad)
+        self.b_raw = bias
+
+    def f16_scale(self):
+        return self.F16_W_SCALE
+
+    def acc_scale(self):
+        return 1.0 / (F16_ACT_SCALE * self.F16_W_SCALE)
+
+    def _pack(self, BN, fp16, buf):
+        w = self.weight.detach()
+        co, ci = w.shape[0], w.shape[1]
+        check(lib().zt_pack_tc_weights_f32(_p(w), co, ci, self.kh, self.kw, self.cin, int(self.dgrad), BN, int(fp16),
+                                           self.F16_W_SCALE if fp16 else 1.0, _p(buf), _stream()), "pack_tc_weights")
+
+    def tc_pack(self, BN, fp16=False):
+        key = (BN, bool(fp16))
+        buf = self._bufs.get(key)
+        if buf is None:
+            nt, ng = (self.cout + BN - 1) // BN, (self.cin + 63) // 64
+            buf = torch.empty(nt * ng * self.kh * self.kw * 2 * BN * 128, dtype=torch.uint8, device=self.weight.device)
+            self._bufs[key] = buf
+            self._pack(BN, fp16, buf)
+        return buf
+
+    def repack(self):
+        for (BN, fp16), buf in self._bufs.items():
+            self._pack(BN, fp16, buf)
+
+
 class RowsAsWeights:
     """Device rows [R][C] used as the weights of a 1x1 tensor-core convolution with cout = R (the
     all-pairs correlation corr.py:52-60: weights = fmap2, re-packed on the device every frame)."""
+    dynamic = True
 
     def __init__(self, R, Cn, BN, device):
         self.kh = self.kw = 1
