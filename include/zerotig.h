@@ -229,6 +229,19 @@ int zt_conv3x3_n2_f32(const float* in, int in_cs, int C, const float* weight, co
 int zt_flow_head2_update_f32(const float* in, int in_cs, int C, const float* weight, const float* bias,
                              float* coords1, float* f1, int f1_cs, float* f2, int f2_cs, int H, int W, void* stream);
 
+/* Convolution weight gradient on the tensor cores (train.py:129 loss.backward(); the nn.Conv2d layers of
+ * model/model.py:15-81): dW[kh][kw][cin_p][w_cs] (fp32, accumulated with atomics) += sum over pixels p of
+ * X[p + tap][ci] * G[p][co].  X (layer input) and G (gradient of the layer output) are NHWC bf16 hi/lo pairs
+ * ([H*W][x_cs], [H*W][g_cs]; zt_split_bf16_hilo; strides multiples of 8): TMA-fed tcgen05 with MN-major operands,
+ * K = pixels, three-term hi/lo products, fp32 accumulation in TMEM across all tiles of a persistent CTA.
+ * 1x1 or 3x3 (zero padding k/2, stride 1), cin <= 64, cout <= 64. */
+/* the operand conversion of zt_conv2d_wgrad_tc: fp32 [M][in_rs] -> bf16 hi / lo [M][out_rs] for C channels (C % 4 == 0);
+ * colsum (may be NULL): colsum[c] += sum_m in[m][c] = the bias gradient when `in` is the output gradient */
+int zt_split_bf16_hilo_colsum(const float* in, int in_rs, void* hi, void* lo, int out_rs, int C, int64_t M, float* colsum,
+                              void* stream);
+int zt_conv2d_wgrad_tc(const void* Xhi, const void* Xlo, int x_cs, const void* Ghi, const void* Glo, int g_cs,
+                       float* dW, int H, int W, int kh, int kw, int cin, int cout, int cin_p, int w_cs, void* stream);
+
 /* ---- RAFT update block, all iterations of a frame pair in ONE persistent cooperative kernel ----
  * Replaces the loop body of RAFT.forward, model/RAFT/raft.py:111-120: CorrBlock.__call__ (corr.py:29-50),
  * BasicUpdateBlock.forward (update.py:127-136: BasicMotionEncoder :89-97, SepConvGRU :45-60, FlowHead :13-14) and

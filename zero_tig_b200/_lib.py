@@ -114,6 +114,8 @@ SIGNATURES = {
     "zt_act_bwd_nhwc_f32": [P, I, P, I, I, I, L, P],
     "zt_bn_train_bwd_nhwc_f32": [P, I, P, I, P, P, P, P, I, I, F, P, I, P, P, P],
     "zt_conv2d_wgrad_nhwc_f32": [P, I, P, I, P, P, I, I, I, I, I, I, I, I, I, P],
+    "zt_split_bf16_hilo_colsum": [P, I, P, P, I, I, L, P, P],
+    "zt_conv2d_wgrad_tc": [P, P, I, P, P, I, P, I, I, I, I, I, I, I, I, P],
     "zt_clip_adam_f32": [P, P, P, P, L, P, F, F, F, F, F, F, F, I, P],
     "zt_last_error": [],
     "zt_version": [],

@@ -611,7 +611,33 @@ class WGrad:
         self.dw.zero_()
         self.db.zero_()
 
+    # tensor-core path (csrc/wgrad_tc.cu): 1x1 / 3x3 'same' convolutions with cin, cout <= 64 - every layer of the three
+    # Retinex nets.  ZT_WGRAD_TC=0 keeps the fp32 FFMA kernel.
+    TC = int(__import__("os").environ.get("ZT_WGRAD_TC", "1"))
+    _scratch = {}
+
+    @classmethod
+    def _hilo(cls, tag, M, cs, device):
+        key = (tag, str(device))
+        t = cls._scratch.get(key)
+        if t is None or t.numel() < 2 * M * cs:
+            t = torch.empty(2 * M * cs, dtype=torch.bfloat16, device=device)
+            cls._scratch[key] = t
+        return t[:M * cs], t[M * cs:2 * M * cs]
+
     def accumulate(self, X, x_cs, G, g_cs, H, W, pad):
+        if (self.TC and (self.kh, self.kw) in ((1, 1), (3, 3)) and pad == (self.kh // 2, self.kw // 2) and
+                self.cin <= 64 and self.cout <= 64):
+            M = H * W
+            cx, cg = (self.cin + 3) // 4 * 4, (self.cout + 3) // 4 * 4
+            xs, gs = (cx + 7) // 8 * 8, (cg + 7) // 8 * 8
+            xh, xl = self._hilo("x", M, xs, X.device)
+            gh, gl = self._hilo("g", M, gs, X.device)
+            check(lib().zt_split_bf16_hilo_colsum(_p(X), x_cs, _p(xh), _p(xl), xs, cx, M, None, _stream()), "split_hilo")
+            check(lib().zt_split_bf16_hilo_colsum(_p(G), g_cs, _p(gh), _p(gl), gs, cg, M, _p(self.db), _stream()), "split_hilo")
+            check(lib().zt_conv2d_wgrad_tc(_p(xh), _p(xl), xs, _p(gh), _p(gl), gs, _p(self.dw), H, W, self.kh, self.kw,
+                                           self.cin, self.cout, self.cin_p, self.w_cs, _stream()), "wgrad_tc")
+            return
         check(lib().zt_conv2d_wgrad_nhwc_f32(_p(X), x_cs, _p(G), g_cs, _p(self.dw), _p(self.db), H, W, self.kh, self.kw,
                                              pad[0], pad[1], self.cin_p, self.cout, self.w_cs, _stream()), "wgrad")
 
