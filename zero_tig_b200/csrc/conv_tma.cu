@@ -15,6 +15,7 @@
 // GEMM view: M = 128 pixels (16 rows x 8), N = cout (<= 64), K = taps x 64 channels (cin <= 64).
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <stdlib.h>
 #include <algorithm>
 #include <map>
 #include <mutex>
@@ -30,6 +31,8 @@ constexpr int TM_W_MMA = 8, TM_W_LOAD = 9;
 constexpr int TM_BAR_BYTES = 1024;
 
 struct TmGeom {
+  int single, PW;                         // single = 1: ONE copy of the tile with its halo (PW = 8 + kw - 1 pixels wide), taps are
+                                          // unaligned shifted views of it (as conv_tc.cu); 0: kw pixel-shifted, atom-aligned copies
   int BN, kh, kw, nks, rows;              // rows = TM_TH + kh - 1
   int tiles_x, S, NA, tmem_cols;
   uint32_t copy_bytes, a_stage, w_tap, w_bytes;
@@ -230,8 +233,11 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((BN >> 3) << 17) | (8u << 24);
     const uint64_t desc0 = make_desc(0, 1024u);
     const uint32_t dhi = (uint32_t)(desc0 >> 32), dlo = (uint32_t)desc0;
+    // single-copy mode: 8-pixel row groups of the patch are PW * 128 B apart, a tap is a row offset of (ky * PW + kx)
+    const uint32_t dhiA = g.single ? (uint32_t)(make_desc(0, (uint32_t)g.PW * 128u) >> 32) : dhi;
+    const uint32_t tap_y16 = g.single ? (uint32_t)g.PW * 8u : 64u, tap_x16 = g.single ? 8u : (g.copy_bytes >> 4);
     const uint32_t smA16 = smem_u32(smA) >> 4, smW16 = smem_u32(smW) >> 4;
-    const uint32_t a_stage16 = g.a_stage >> 4, copy16 = g.copy_bytes >> 4, wtap16 = g.w_tap >> 4;
+    const uint32_t a_stage16 = g.a_stage >> 4, wtap16 = g.w_tap >> 4;
     const uint32_t kh = g.kh, kw = g.kw, nks = g.nks;
     mbar_wait(fullW, 0);
     tc_fence_after();
@@ -247,9 +253,9 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
         const uint32_t abase = dlo + smA16 + sa * a_stage16;
         for (uint32_t ky = 0; ky < kh; ++ky) {
           for (uint32_t kx = 0; kx < kw; ++kx, blo += wtap16) {
-            const uint32_t alo = abase + kx * copy16 + ky * 64u;      // ky atoms of 1024 B
+            const uint32_t alo = abase + kx * tap_x16 + ky * tap_y16;      // aligned copies: ky atoms of 1024 B
             for (uint32_t ks = 0; ks < nks; ++ks) {
-              tc_mma_bf16_lh(tmem_d, alo + 2 * ks, dhi, blo + 2 * ks, dhi, idesc, acc);
+              tc_mma_bf16_lh(tmem_d, alo + 2 * ks, dhiA, blo + 2 * ks, dhi, idesc, acc);
               acc = 1;
             }
           }
@@ -275,10 +281,15 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
       for (int t = blockIdx.x; t < S; t += gridDim.x) {
         const int tyi = t / g.tiles_x, txi = t - tyi * g.tiles_x;
         mbar_wait(emptyA(sa), pa);
-        mbar_arrive_expect_tx(fullA(sa), g.a_stage);
-        for (int kx = 0; kx < g.kw; ++kx)
-          tma_load_3d(smem_u32(smA + sa * g.a_stage + kx * g.copy_bytes), &tmap, 0, txi * TM_TW + kx - a.pw,
-                      tyi * TM_TH - a.ph, fullA(sa));
+        if (g.single) {
+          mbar_arrive_expect_tx(fullA(sa), g.copy_bytes);
+          tma_load_3d(smem_u32(smA + sa * g.a_stage), &tmap, 0, txi * TM_TW - a.pw, tyi * TM_TH - a.ph, fullA(sa));
+        } else {
+          mbar_arrive_expect_tx(fullA(sa), g.a_stage);
+          for (int kx = 0; kx < g.kw; ++kx)
+            tma_load_3d(smem_u32(smA + sa * g.a_stage + kx * g.copy_bytes), &tmap, 0, txi * TM_TW + kx - a.pw,
+                        tyi * TM_TH - a.ph, fullA(sa));
+        }
         if (++sa == (uint32_t)NA) { sa = 0; pa ^= 1; }
       }
     }
@@ -395,18 +406,18 @@ static EncodeTiledFn encode_fn() {
   return fn;
 }
 static std::mutex g_tm_mu;
-static std::map<std::tuple<const void*, int, int, int, int>, CUtensorMap> g_tm_cache;
+static std::map<std::tuple<const void*, int, int, int, int, int>, CUtensorMap> g_tm_cache;
 
-static int get_tensor_map(const void* base, int C, int W, int H, int rows, CUtensorMap* out) {
+static int get_tensor_map(const void* base, int C, int W, int H, int rows, int box_w, CUtensorMap* out) {
   std::lock_guard<std::mutex> lk(g_tm_mu);
-  auto key = std::make_tuple(base, C, W, H, rows);
+  auto key = std::make_tuple(base, C, W, H, rows, box_w);
   auto it = g_tm_cache.find(key);
   if (it != g_tm_cache.end()) { *out = it->second; return ZT_OK; }
   EncodeTiledFn fn = encode_fn();
   if (!fn) { set_error("conv_bf16_tma: cuTensorMapEncodeTiled is unavailable (no CUDA driver)"); return ZT_ERR_CUDA; }
   const cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H};
   const cuuint64_t strides[2] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2};
-  const cuuint32_t box[3] = {64u, (cuuint32_t)TM_TW, (cuuint32_t)rows};
+  const cuuint32_t box[3] = {64u, (cuuint32_t)box_w, (cuuint32_t)rows};
   const cuuint32_t estr[3] = {1u, 1u, 1u};
   CUtensorMap m;
   const CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
@@ -479,18 +490,29 @@ extern "C" int zt_conv2d_bf16_tma(const ZtConvBf16* dp, void* stream) {
   g.rows = TM_TH + d.kh - 1;
   g.tiles_x = ceil_div(d.W, TM_TW);
   g.S = g.tiles_x * ceil_div(d.H, TM_TH);
-  g.copy_bytes = (uint32_t)g.rows * 1024u;
-  g.a_stage = g.copy_bytes * d.kw;
+  // One copy with halo + unaligned tap views costs more per MMA (operand rows straddle swizzle atoms) but a third of
+  // the TMA bytes: the thin layers (K = 16 per tap, or few output channels) are bound by the copies, the 64 -> 64
+  // blocks by the MMAs.  ZT_TMA_SINGLE: -1 = never, else "use it when cin * BN <= value" (default 48 * 48).
+  static const int single_thr = getenv("ZT_TMA_SINGLE") ? atoi(getenv("ZT_TMA_SINGLE")) : 48 * 48;
+  g.single = (d.kw == 3 && single_thr >= 0 && d.cin * g.BN <= single_thr) ? 1 : 0;
+  g.PW = TM_TW + d.kw - 1;
+  if (g.single) {
+    g.copy_bytes = (uint32_t)(g.rows * g.PW) * 128u;                      // bytes the TMA box writes
+    g.a_stage = (g.copy_bytes + 1023u) / 1024u * 1024u;
+  } else {
+    g.copy_bytes = (uint32_t)g.rows * 1024u;
+    g.a_stage = g.copy_bytes * d.kw;
+  }
   g.w_tap = (uint32_t)g.BN * 128u;
   g.w_bytes = g.w_tap * d.kh * d.kw;
   g.tmem_cols = 32;
   while (g.tmem_cols < 2 * g.BN) g.tmem_cols <<= 1;
   const size_t budget = 226 * 1024 - TM_BAR_BYTES - g.w_bytes - (d.head_n ? 6 * 1024 : 0);     // static smem of OUT = 3
-  g.NA = (int)std::min<size_t>(4, budget / g.a_stage);
+  g.NA = (int)std::min<size_t>(g.single ? 6 : 4, budget / g.a_stage);
   ZT_REQUIRE(g.NA >= 2, "conv_bf16_tma: tile does not fit shared memory");
   const size_t smem = TM_BAR_BYTES + (size_t)g.NA * g.a_stage + g.w_bytes;
   CUtensorMap tmap;
-  if (int e = get_tensor_map(d.in, d.cin, d.W, d.H, g.rows, &tmap)) return e;
+  if (int e = get_tensor_map(d.in, d.cin, d.W, d.H, g.rows, g.single ? g.PW : TM_TW, &tmap)) return e;
   TmArgs a;
   a.weight = (const uint8_t*)d.weight; a.bias = d.bias; a.out = d.out; a.out_cs = d.out_cs;
   a.res = (const __nv_bfloat16*)d.res; a.res_cs = d.res_cs;

@@ -384,13 +384,12 @@ __global__ void bn_bwd_reduce_kernel(const float* __restrict__ x, int x_cs, cons
                                      double* __restrict__ red) {
   // thread t owns channel t % C; rows strided by blockDim.x / C
   const int c = threadIdx.x % C, r0 = threadIdx.x / C, rstep = blockDim.x / C;
-  if (r0 >= rstep) return;
   const double mean = stats[c * 2] / HW;
   double var = stats[c * 2 + 1] / HW - mean * mean;
   var = var < 0 ? 0 : var;
   const float rstd = (float)(1.0 / sqrt(var + (double)eps)), mu = (float)mean;
   const float ga = gamma[c], be = beta[c];
-  const int p0 = blockIdx.x * ppb, p1 = min(HW, p0 + ppb);
+  const int p0 = blockIdx.x * ppb, p1 = r0 >= rstep ? 0 : min(HW, p0 + ppb);
   double s0 = 0.0, s1 = 0.0;
   for (int p = p0 + r0; p < p1; p += rstep) {
     const float xh = (x[(int64_t)p * x_cs + c] - mu) * rstd;
@@ -399,8 +398,16 @@ __global__ void bn_bwd_reduce_kernel(const float* __restrict__ x, int x_cs, cons
     s0 += (double)dy;
     s1 += (double)(dy * xh);
   }
-  atomicAdd(red + c * 2, s0);
-  atomicAdd(red + c * 2 + 1, s1);
+  // block-level reduction first: hundreds of blocks adding fp64 values into the same 2*C addresses serialise in L2
+  __shared__ double rs[256][2];
+  rs[threadIdx.x][0] = s0;
+  rs[threadIdx.x][1] = s1;
+  __syncthreads();
+  if (r0 == 0) {
+    for (int r = 1; r < rstep; ++r) { s0 += rs[r * C + c][0]; s1 += rs[r * C + c][1]; }
+    atomicAdd(red + c * 2, s0);
+    atomicAdd(red + c * 2 + 1, s1);
+  }
 }
 // pass 2: dx = gamma * rstd * (dy - mean(dy) - xhat * mean(dy * xhat))
 __global__ void bn_bwd_apply_kernel(const float* __restrict__ x, int x_cs, const float* __restrict__ dout, int d_cs,
