@@ -113,6 +113,17 @@ int zt_instnorm_nhwc_f32(const float* x, int x_cs, float* out, int out_cs,
                          const float* res, int res_cs, double* stats,
                          int B, int HW, int C, float eps, int relu_inner, int relu_outer,
                          void* stream);
+/* Allocation-free variant of zt_instnorm_nhwc_f32.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments minus `stats`: the fp64 statistics live in a file-scope static __device__ array of
+ * 2 * ZT_INSTNORM_NOALLOC_MAX_BC doubles (16 KB, held by every GPU that loads the library until exit); the call
+ * allocates nothing.  B * C > ZT_INSTNORM_NOALLOC_MAX_BC is rejected with ZT_ERR_ARG.  All calls on a device share
+ * the array (cleared at the start of each call): calls that overlap on the GPU (different streams) race. */
+#define ZT_INSTNORM_NOALLOC_MAX_BC 1024
+int zt_instnorm_nhwc_f32_noalloc(const float* x, int x_cs, float* out, int out_cs,
+                                 const float* res, int res_cs,
+                                 int B, int HW, int C, float eps, int relu_inner, int relu_outer,
+                                 void* stream);
 
 /* ---- RAFT correlation: corr.py:13-27,52-60 ---------------------------------------------- */
 /* out[c][r] = in[r][c]; out row stride out_rs (>= R) */

@@ -69,6 +69,7 @@ SIGNATURES = {
     "zt_pack_tc_rows_f32": [P, I, I, I, I, P, P],
     "zt_pack_tc_weights_f32": [P, I, I, I, I, I, I, I, I, F, P, P],
     "zt_instnorm_nhwc_f32": [P, I, P, I, P, I, P, I, I, I, F, I, I, P],
+    "zt_instnorm_nhwc_f32_noalloc": [P, I, P, I, P, I, I, I, I, F, I, I, P],
     "zt_transpose_f32": [P, I, I, I, P, I, P],
     "zt_avgpool2_f32": [P, P, L, I, I, P],
     "zt_corr_lookup_f32": [P, P, P, P, IP, IP, P, P, I, I, P],

@@ -3,6 +3,7 @@
 // Two kernels: per-(image,channel) sum / sum-of-squares accumulated in fp64 (one pass,
 // no cancellation problem), then a fused normalise [+relu] [+residual] [+relu] pass.
 #include <algorithm>
+#include <mutex>
 #include "common.cuh"
 
 namespace zt {
@@ -164,6 +165,61 @@ extern "C" int zt_instnorm_nhwc_f32(const float* x, int x_cs, float* out, int ou
   const int blocks = (int)std::min<int64_t>(ceil_div64(total4, 256), 8 * kNumSMs);
   ZT_CUDA(launch_pdl(instnorm_apply_kernel, dim3(blocks), dim3(256), (size_t)B * C * sizeof(float2), st, x, x_cs, out, out_cs,
                      res, res_cs, stats, HW, C, B * C, eps, relu_inner, relu_outer, total4));
+  return check_launch("instnorm_apply_kernel");
+}
+
+// ---- allocation-free variant ---------------------------------------------------------------------------------------
+// Same two kernels, but the fp64 statistics live in a file-scope device array instead of a caller-provided buffer,
+// for callers that cannot allocate (CUDA graph capture, tight serving loops).  No counterpart in the reference.
+// Every GPU that loads the library holds the 16 KB until exit.  All calls on a device share the array: it is cleared
+// at the start of every call, and two calls that overlap on the GPU (different streams) race on it.
+namespace zt {
+static __device__ __align__(256) double g_instnorm_scratch[2 * ZT_INSTNORM_NOALLOC_MAX_BC];
+
+// In host code `g_instnorm_scratch` is only a host-side stand-in for the symbol, not a device address: resolve it
+// once per device (with that device current) and cache the pointer.
+static int instnorm_scratch_ptr(double** out) {
+  constexpr int kMaxDev = 64;
+  static std::mutex mu;
+  static double* ptrs[kMaxDev] = {};
+  int dev = -1;
+  ZT_CUDA(cudaGetDevice(&dev));
+  ZT_REQUIRE(dev >= 0 && dev < kMaxDev, "instnorm_noalloc: device index %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    double* p = nullptr;
+    ZT_CUDA(cudaGetSymbolAddress((void**)&p, g_instnorm_scratch));
+    ZT_REQUIRE(p != nullptr, "instnorm_noalloc: cudaGetSymbolAddress returned a null pointer");
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return ZT_OK;
+}
+}  // namespace zt
+
+extern "C" int zt_instnorm_nhwc_f32_noalloc(const float* x, int x_cs, float* out, int out_cs, const float* res,
+                                            int res_cs, int B, int HW, int C, float eps, int relu_inner,
+                                            int relu_outer, void* stream) {
+  using namespace zt;
+  ZT_REQUIRE(x && out, "instnorm_noalloc: null pointer");
+  ZT_REQUIRE((C & 3) == 0 && C > 0 && (x_cs & 3) == 0 && (out_cs & 3) == 0 && (!res || (res_cs & 3) == 0),
+             "instnorm_noalloc: C and strides must be multiples of 4 (C=%d)", C);
+  ZT_REQUIRE(B > 0 && HW > 0, "instnorm_noalloc: bad dims");
+  ZT_REQUIRE((int64_t)B * C <= ZT_INSTNORM_NOALLOC_MAX_BC,
+             "instnorm_noalloc: B*C = %lld exceeds the static scratch (ZT_INSTNORM_NOALLOC_MAX_BC = %d); use "
+             "zt_instnorm_nhwc_f32 with a caller-provided stats buffer", (long long)B * C, ZT_INSTNORM_NOALLOC_MAX_BC);
+  double* stats = nullptr;
+  if (int e = instnorm_scratch_ptr(&stats)) return e;
+  cudaStream_t st = (cudaStream_t)stream;
+  ZT_CUDA(cudaMemsetAsync(stats, 0, sizeof(double) * 2 * B * C, st));     // the array keeps the last call's sums
+  const int slabs = max(1, min(ceil_div(HW, 64), (4 * kNumSMs) / B));
+  const int ppb = ceil_div(HW, slabs);
+  instnorm_stats_kernel<<<dim3(ceil_div(HW, ppb), B), 256, 0, st>>>(x, x_cs, stats, HW, C, ppb);
+  if (int e = check_launch("instnorm_stats_kernel")) return e;
+  const int64_t total4 = (int64_t)B * HW * (C >> 2);
+  const int blocks = (int)std::min<int64_t>(ceil_div64(total4, 256), 8 * kNumSMs);
+  ZT_CUDA(launch_pdl(instnorm_apply_kernel, dim3(blocks), dim3(256), (size_t)B * C * sizeof(float2), st, x, x_cs, out,
+                     out_cs, res, res_cs, (const double*)stats, HW, C, B * C, eps, relu_inner, relu_outer, total4));
   return check_launch("instnorm_apply_kernel");
 }
 
