@@ -340,7 +340,12 @@ def classify(c, frame_pixels):
     if name == "wgrad":
         obj, X, x_cs, G, g_cs, Hn, Wn = a[0], a[1], a[2], a[3], a[4], a[5], a[6]
         flops = 2.0 * Hn * Wn * obj.cout * obj.cin * obj.kh * obj.kw
-        return ("conv weight gradient (fp32 FFMA)", flops, 0.0, 4.0 * Hn * Wn * (x_cs + g_cs),
+        pad = a[7] if len(a) > 7 else k.get("pad")
+        tc = bool(obj.TC and (obj.kh, obj.kw) in ((1, 1), (3, 3)) and tuple(pad) == (obj.kh // 2, obj.kw // 2) and
+                  obj.cin <= 64 and obj.cout <= 64)             # the condition of ops.WGrad.accumulate
+        fam = ("conv weight gradient (tcgen05, bf16 hi/lo split, K = pixels; incl. the two split + bias-gradient passes)"
+               if tc else "conv weight gradient (fp32 FFMA)")
+        return (fam, flops, 3.0 * flops if tc else 0.0, 4.0 * Hn * Wn * (x_cs + g_cs),
                 "%dx%d %d->%d @%dx%d" % (obj.kh, obj.kw, obj.cin, obj.cout, Hn, Wn))
     if name in ("instnorm",):
         return "instnorm", 0.0, 0.0, 0.0, ""
