@@ -621,7 +621,7 @@ def run_b200(args):
             bound = "tensor" if top["issued"] > 0 else "hbm"
             roof = roofline_entry(top_name, top, pk, step_us, bound)
             roof["peak_source"] = pk["src"] + (" sustained bf16 throughput" if bound == "tensor" else " copy bandwidth")
-            roof["traffic"] = TRAFFIC.get(top_name)
+            roof["traffic"] = TRAFFIC.get(top_name) if args.config == "1080p" else None      # captured at 1080p only
             roof["timing"] = ("every distinct launch of one steady frame re-timed as %d back-to-back copies in a CUDA graph "
                               "(CUDA events around the replay); shares are relative to one frame chain alone" % 8)
             out["roofline"] = roof
@@ -648,7 +648,11 @@ def run_b200(args):
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the family's dominant kernel from the committed
 # `ncu --set full` capture (profiles/), keyed by family name; None until captured for the current kernel
-TRAFFIC = {}
+TRAFFIC = {
+    # profiles/r02_ncu_raft_update.txt: dram__bytes_read.sum + dram__bytes_write.sum of one launch (1080p, 12 iterations)
+    "raft_update (persistent TMA-fed tcgen05 update block, all 12 iterations)": 78.09e6 + 35.70e6,
+    # profiles/r02_ncu_conv_tma.txt is per layer; the family has no single per-launch figure
+}
 
 
 TRAIN_H, TRAIN_W = 540, 960
