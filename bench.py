@@ -44,6 +44,24 @@ CONFIGS = {
 }
 
 
+_JSON_OUT = None
+
+
+def claim_stdout():
+    """stdout must carry exactly ONE JSON line, but libraries write to file descriptor 1 too (NCCL prints its version
+    banner there): keep a private duplicate of fd 1 for the JSON line and point fd 1 at stderr for everything else."""
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit_line(obj):
+    f = _JSON_OUT or sys.stdout
+    f.write(json.dumps(obj) + "\n")
+    f.flush()
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -143,14 +161,14 @@ def run_reference(args):
             break
     fps = done / t_total
     sample = "%d steady-state frames (of %d requested; %.0f s budget)" % (done, args.steps, budget)
-    print(json.dumps({
+    emit_line({
         "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus, "steps": done,
         "warmup": warm, "ms_per_step": 1e3 * t_total / done, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_string(args.config), "arm": "CPU oracle port of the reference (oracle/zt_oracle.py)"},
         "cpu_baseline": {"value": fps, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0}))
+        "gpu_launches": 0})
 
 
 def cpu_baseline(sd, cfg):
@@ -415,7 +433,9 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        # a collective mismatch must cost two minutes, not the default ten
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
     _lib.lib()
     H, W, dataset, n_frames, cfg_tag = CONFIGS[args.config]
     # S frame-range shards of this rank's clip (each: own model replica, recurrent state and stream; round-robin
@@ -568,7 +588,8 @@ def run_b200(args):
 
     train = None
     if not args.no_train and args.config == "1080p":
-        train = train_step_bench(dev, world, sd, profile=(rank == 0 and not args.no_profile))
+        # every rank runs the extra profiled step (it holds the gradient all-reduce); only rank 0 records it
+        train = train_step_bench(dev, world, sd, profile=not args.no_profile, record=(rank == 0))
 
     out = None
     if rank == 0:
@@ -643,7 +664,7 @@ def run_b200(args):
         dist.barrier()
         dist.destroy_process_group()
     if out is not None:
-        print(json.dumps(out))
+        emit_line(out)
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the family's dominant kernel from the committed
@@ -658,7 +679,7 @@ TRAFFIC = {
 TRAIN_H, TRAIN_W = 540, 960
 
 
-def train_step_bench(dev, world, sd, steps=8, warmup=2, profile=False):
+def train_step_bench(dev, world, sd, steps=8, warmup=2, profile=False, record=True):
     """configs[2]: zero-shot training steps (Network._loss forward incl. RAFT + warp, CUDA backward, one
     all-reduce of the flat gradient buffer when world > 1, fused clip + Adam) on a synthetic 960x540 clip,
     one clip per rank.  The loss of the first two frames (before any optimiser step) is checked against the value
@@ -720,7 +741,10 @@ def train_step_bench(dev, world, sd, steps=8, warmup=2, profile=False):
            "gpu_launches_per_step": int((_lib.launch_count() - l0) // steps), "steps": steps, "warmup": warmup + 1,
            "last_loss": float(loss.detach()), "loss_check_vs_reference": check,
            "collective": "1 x all_reduce(sum) of 92620 fp32 per step" if world > 1 else "none (1 GPU)"}
-    if profile:
+    if profile and not record:
+        step(warmup + steps)                 # keeps the collective sequence identical on every rank
+        torch.cuda.synchronize()
+    if profile and record:
         from zero_tig_b200 import ops
         pk = peaks()
         with KernelProfiler(ops) as kp:
@@ -761,6 +785,7 @@ def main():
     ap.add_argument("--no-profile", action="store_true", help="skip the per-kernel roofline pass")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    claim_stdout()
     if args.impl == "reference":
         run_reference(args)
     else:
