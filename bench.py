@@ -79,7 +79,34 @@ class ClockSampler:
         self.rows, self.stop, self.index = [], False, index
         self.t = threading.Thread(target=self.run, daemon=True)
 
+    # NVML clocks-event-reason bits (nvml.h): sw_power_cap 0x4, hw_slowdown 0x8, sw_thermal 0x20, hw_thermal 0x40
+    BITS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
+
+    def run_nvml(self):
+        """Same four fields through NVML (one library call per sample instead of one nvidia-smi process: eight ranks
+        polling nvidia-smi at once got 4 samples in 2.5 s).  Returns False when NVML is unavailable."""
+        try:
+            import pynvml as N
+            N.nvmlInit()
+            h = N.nvmlDeviceGetHandleByIndex(self.index)
+            mx = N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM)
+            reasons = getattr(N, "nvmlDeviceGetCurrentClocksEventReasons", None) or N.nvmlDeviceGetCurrentClocksThrottleReasons
+            reasons(h)
+        except Exception:
+            return False
+        while not self.stop:
+            try:
+                r = reasons(h)
+                self.rows.append([str(N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM)), str(mx)] +
+                                 ["Active" if r & bit else "Not Active" for _, bit in self.BITS])
+            except Exception:
+                pass
+            time.sleep(0.05)
+        return True
+
     def run(self):
+        if os.environ.get("ZT_CLOCKS_NVML", "1") != "0" and self.run_nvml():
+            return
         while not self.stop:
             try:
                 o = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
