@@ -29,6 +29,7 @@ constexpr int TM_TW = 8, TM_TH = 16;
 constexpr int TM_THREADS = 320;           // warps 0-7 epilogue, 8 MMA issuer, 9 TMA / weight loader
 constexpr int TM_W_MMA = 8, TM_W_LOAD = 9;
 constexpr int TM_BAR_BYTES = 1024;
+constexpr int TM_STG_BYTES = 8 * 2048;   // epilogue staging: 32 pixels x 64 B per epilogue warp
 
 struct TmGeom {
   int single, PW;                         // single = 1: ONE copy of the tile with its halo (PW = 8 + kw - 1 pixels wide), taps are
@@ -36,6 +37,8 @@ struct TmGeom {
   int BN, kh, kw, nks, rows;              // rows = TM_TH + kh - 1
   int tiles_x, S, NA, tmem_cols;
   uint32_t copy_bytes, a_stage, w_tap, w_bytes;
+  int coal;                               // bf16 outputs: transpose the tile through shared memory so global stores / residual
+                                          // loads touch 8 lines per instruction instead of 32 (TM_STG_BYTES after the weights)
 };
 struct TmArgs {
   const uint8_t* weight;                  // [tap][BN][128 B] bf16, swizzled
@@ -63,6 +66,27 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 // OUT: 0 = bf16 out, 1 = bf16 out with residual (out = res + act(v)), 2 = fp32 out (cout <= 8),
 //      3 = fp32 out of a fused 1x1 head: out[h] = head_b[h] + sum_c head_w[h][c] * act(v[c] + bias[c]), h < out_cs
 //          (the 48 -> 3 / 48 -> 6 heads of the denoisers, model.py:27,43: the 48-channel activation never goes to HBM)
+// The MMAs of one pixel tile of a 3x3 convolution, fully unrolled: 9 taps x NKS 16-channel k-steps.  The generic loop
+// below (runtime kh / kw / nks read from the parameter struct) costs ~25 dependent scalar instructions per MMA in the
+// single issuing thread - 225 clk per MMA on the 16-channel layers, 100 clk on the 64-channel ones, more than the
+// MMA itself (ncu source page, profiles/r02_ncu_conv_tma.txt); here an MMA is two adds away from the previous one.
+template <int NKS>
+__device__ __forceinline__ void tm_issue_3x3(uint32_t tmem_d, uint32_t abase, uint32_t bbase, uint32_t tap_x16,
+                                             uint32_t tap_y16, uint32_t wtap16, uint32_t dhiA, uint32_t dhi,
+                                             uint32_t idesc) {
+#pragma unroll
+  for (int ky = 0; ky < 3; ++ky) {
+#pragma unroll
+    for (int kx = 0; kx < 3; ++kx) {
+      const uint32_t alo = abase + (uint32_t)kx * tap_x16 + (uint32_t)ky * tap_y16;
+      const uint32_t blo = bbase + (uint32_t)(ky * 3 + kx) * wtap16;
+#pragma unroll
+      for (int ks = 0; ks < NKS; ++ks)
+        tc_mma_bf16_lh(tmem_d, alo + 2u * ks, dhiA, blo + 2u * ks, dhi, idesc, (ky | kx | ks) ? 1u : 0u);
+    }
+  }
+}
+
 template <int OUT, int ACT>
 __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_constant__ CUtensorMap tmap,
                                                                  const TmArgs a, const TmGeom g) {
@@ -117,6 +141,8 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
     float bias[32];
 #pragma unroll
     for (int i = 0; i < 32; ++i) bias[i] = (a.bias && c0 + i < a.cout) ? __ldg(a.bias + c0 + i) : 0.f;
+    const bool coal = OUT <= 1 && g.coal != 0;
+    uint4* stg = reinterpret_cast<uint4*>(smW + g.w_bytes + (size_t)warp * 2048);
     uint32_t lt = 0;
     for (int t = blockIdx.x; t < S; t += gridDim.x, ++lt) {
       const int tyi = t / g.tiles_x, txi = t - tyi * g.tiles_x;
@@ -125,7 +151,18 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
       const int64_t pix = (int64_t)oy * a.W + ox;
       const uint32_t buf = lt & 1;
       uint4 rv[4];
-      if (OUT == 1) {
+      // coalesced mapping: instruction i, lane l <-> pixel (tile row quad*4 + i, x = l >> 2), 16-byte chunk l & 3 of this half:
+      // four lanes cover the 64 contiguous bytes of a pixel, a warp instruction touches 8 lines (thread = pixel: 32)
+      const int cx = txi * TM_TW + (lane >> 2), cch = c0 + 8 * (lane & 3);
+      const bool cok = coal && cx < a.W && cch < a.cout;
+      if (OUT == 1 && coal) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int cy = tyi * TM_TH + quad * 4 + i;
+          rv[i] = make_uint4(0u, 0u, 0u, 0u);
+          if (cok && cy < a.H) rv[i] = __ldg(reinterpret_cast<const uint4*>(a.res + ((int64_t)cy * a.W + cx) * a.res_cs + cch));
+        }
+      } else if (OUT == 1) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           rv[j] = make_uint4(0u, 0u, 0u, 0u);
@@ -189,6 +226,50 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
         asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");     // part_s may be overwritten by the next tile
         continue;
       }
+      if (OUT <= 1 && coal) {
+        if (!has_cols) continue;                                     // warp-uniform
+        // staging rows of 64 B, 16-byte chunk position XOR ((row >> 1) & 3): conflict-free for both access patterns
+        uint4* own = stg + lane * 4;
+        const uint32_t swz = (lane >> 1) & 3;
+        if (OUT == 1) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int pr = 8 * i + (lane >> 2);
+            stg[pr * 4 + ((lane & 3) ^ ((pr >> 1) & 3))] = rv[i];
+          }
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 4; ++j) rv[j] = own[j ^ swz];
+          __syncwarp();
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float r[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) r[e] = tm_act(__uint_as_float(v[8 * j + e]) + bias[8 * j + e], ACT);
+          if (OUT == 1) {
+            const uint32_t rw[4] = {rv[j].x, rv[j].y, rv[j].z, rv[j].w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&rw[e]);
+              r[2 * e] += __low2float(h);
+              r[2 * e + 1] += __high2float(h);
+            }
+          }
+          own[j ^ swz] = make_uint4(pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]),
+                                    pack_bf16x2(r[6], r[7]));
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int pr = 8 * i + (lane >> 2), cy = tyi * TM_TH + quad * 4 + i;
+          const uint4 q = stg[pr * 4 + ((lane & 3) ^ ((pr >> 1) & 3))];
+          if (cok && cy < a.H)
+            *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(a.out) + ((int64_t)cy * a.W + cx) * a.out_cs + cch) = q;
+        }
+        __syncwarp();                                                // the next tile overwrites the staging rows
+        continue;
+      }
       if (!ok) continue;
       if (OUT == 2) {
         float* o = reinterpret_cast<float*>(a.out) + pix * a.out_cs;
@@ -239,6 +320,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
     const uint32_t smA16 = smem_u32(smA) >> 4, smW16 = smem_u32(smW) >> 4;
     const uint32_t a_stage16 = g.a_stage >> 4, wtap16 = g.w_tap >> 4;
     const uint32_t kh = g.kh, kw = g.kw, nks = g.nks;
+    const uint32_t issue3x3 = (kh == 3 && kw == 3 && (nks == 1 || nks == 3 || nks == 4)) ? nks : 0u;
     mbar_wait(fullW, 0);
     tc_fence_after();
     uint32_t lt = 0, sa = 0, pa = 0;
@@ -251,6 +333,10 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
         const uint32_t tmem_d = tmem_base + buf * BN;
         uint32_t acc = 0, blo = dlo + smW16;
         const uint32_t abase = dlo + smA16 + sa * a_stage16;
+        if (issue3x3 == 1) tm_issue_3x3<1>(tmem_d, abase, blo, tap_x16, tap_y16, wtap16, dhiA, dhi, idesc);
+        else if (issue3x3 == 3) tm_issue_3x3<3>(tmem_d, abase, blo, tap_x16, tap_y16, wtap16, dhiA, dhi, idesc);
+        else if (issue3x3 == 4) tm_issue_3x3<4>(tmem_d, abase, blo, tap_x16, tap_y16, wtap16, dhiA, dhi, idesc);
+        else
         for (uint32_t ky = 0; ky < kh; ++ky) {
           for (uint32_t kx = 0; kx < kw; ++kx, blo += wtap16) {
             const uint32_t alo = abase + kx * tap_x16 + ky * tap_y16;      // aligned copies: ky atoms of 1024 B
@@ -507,10 +593,14 @@ extern "C" int zt_conv2d_bf16_tma(const ZtConvBf16* dp, void* stream) {
   g.w_bytes = g.w_tap * d.kh * d.kw;
   g.tmem_cols = 32;
   while (g.tmem_cols < 2 * g.BN) g.tmem_cols <<= 1;
-  const size_t budget = 226 * 1024 - TM_BAR_BYTES - g.w_bytes - (d.head_n ? 6 * 1024 : 0);     // static smem of OUT = 3
+  // ZT_TMA_COALESCE=0 keeps the thread-per-pixel stores (every lane of a store instruction in a different 128-byte line)
+  static const int coalesce = getenv("ZT_TMA_COALESCE") ? atoi(getenv("ZT_TMA_COALESCE")) : 1;
+  g.coal = (coalesce && !d.out_f32 && !d.head_n) ? 1 : 0;
+  const size_t stg_bytes = g.coal ? TM_STG_BYTES : 0;
+  const size_t budget = 226 * 1024 - TM_BAR_BYTES - g.w_bytes - stg_bytes - (d.head_n ? 6 * 1024 : 0);   // static smem of OUT = 3
   g.NA = (int)std::min<size_t>(g.single ? 6 : 4, budget / g.a_stage);
   ZT_REQUIRE(g.NA >= 2, "conv_bf16_tma: tile does not fit shared memory");
-  const size_t smem = TM_BAR_BYTES + (size_t)g.NA * g.a_stage + g.w_bytes;
+  const size_t smem = TM_BAR_BYTES + (size_t)g.NA * g.a_stage + g.w_bytes + stg_bytes;
   CUtensorMap tmap;
   if (int e = get_tensor_map(d.in, d.cin, d.W, d.H, g.rows, g.single ? g.PW : TM_TW, &tmap)) return e;
   TmArgs a;
