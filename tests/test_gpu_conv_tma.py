@@ -96,7 +96,7 @@ def test_pack_nhwc_bf16_four_pixel_path(nsrc, cs):
 
 
 
-@pytest.mark.parametrize("hn,H,W", [(3, 37, 45), (6, 50, 70), (6, 16, 8), (3, 270, 480)])
+@pytest.mark.parametrize("hn,H,W", [(3, 37, 45), (6, 50, 70), (6, 16, 8), (3, 270, 480), (8, 33, 40), (5, 20, 24), (1, 17, 9)])
 def test_conv_bf16_tma_fused_head(hn, H, W):
     """conv2 (3x3, 48 -> 48, LeakyReLU) with conv3 (1x1, 48 -> 3 / 6) applied in its epilogue (model.py:26-27,42-43)
     against torch on the same bf16-rounded conv2 operands.  The 48-channel activation stays in fp32 registers, so the

@@ -50,6 +50,7 @@ struct TmArgs {
   int H, W, cout, ph, pw;
   const float* head_w;                    // OUT = 3: fp32 [8][64] weights of a fused 1x1 head (zero padded), bias [8]
   const float* head_b;
+  int head_n;                             // real head count (<= 8): the epilogue multiplies 4, 6 or 8 columns of head_w
 };
 
 __device__ __forceinline__ float tm_act(float v, int act) {
@@ -66,6 +67,25 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 // OUT: 0 = bf16 out, 1 = bf16 out with residual (out = res + act(v)), 2 = fp32 out (cout <= 8),
 //      3 = fp32 out of a fused 1x1 head: out[h] = head_b[h] + sum_c head_w[h][c] * act(v[c] + bias[c]), h < out_cs
 //          (the 48 -> 3 / 48 -> 6 heads of the denoisers, model.py:27,43: the 48-channel activation never goes to HBM)
+// two TMEM loads in flight, one wait (each tcgen05.ld + wait round trip is ~100 clk of epilogue latency)
+__device__ __forceinline__ void tm_ld16_nowait(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+}
+#define ZT_TM_R16(a) "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(a[4]), "+r"(a[5]), "+r"(a[6]), "+r"(a[7]), \
+                     "+r"(a[8]), "+r"(a[9]), "+r"(a[10]), "+r"(a[11]), "+r"(a[12]), "+r"(a[13]), "+r"(a[14]), "+r"(a[15])
+__device__ __forceinline__ void tm_ld_wait2(uint32_t (&a)[16], uint32_t (&b)[16]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : ZT_TM_R16(a), ZT_TM_R16(b) :: "memory");
+}
+// (p0, p1) += x * (w0, w1) as one packed FFMA2 (two IEEE fp32 FMAs: the same bits as two FFMAs)
+__device__ __forceinline__ void tm_fma2(float& p0, float& p1, float x, float w0, float w1) {
+  asm("{\n\t.reg .b64 xx, ww, pp;\n\tmov.b64 xx, {%2, %2};\n\tmov.b64 ww, {%3, %4};\n\tmov.b64 pp, {%0, %1};\n\t"
+      "fma.rn.f32x2 pp, xx, ww, pp;\n\tmov.b64 {%0, %1}, pp;\n\t}" : "+f"(p0), "+f"(p1) : "f"(x), "f"(w0), "f"(w1));
+}
+
 // The MMAs of one pixel tile of a 3x3 convolution, fully unrolled: 9 taps x NKS 16-channel k-steps.  The generic loop
 // below (runtime kh / kw / nks read from the parameter struct) costs ~25 dependent scalar instructions per MMA in the
 // single issuing thread - 225 clk per MMA on the 16-channel layers, 100 clk on the 64-channel ones, more than the
@@ -115,7 +135,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __shared__ __align__(16) float hw_s[OUT == 3 ? 8 * 64 : 4];
-  __shared__ __align__(16) float part_s[OUT == 3 ? 4 * 32 * 8 : 4];
+  __shared__ __align__(16) float part_s[OUT == 3 ? 2 * 4 * 32 * 8 : 4];      // double buffered by tile parity
   if (OUT == 3) {
     // constants, fetched before the dependency wait; stored channel-major so one channel's 8 weights are two LDS.128
     for (int i = threadIdx.x; i < 8 * 64; i += TM_THREADS) hw_s[(i & 63) * 8 + (i >> 6)] = __ldg(a.head_w + i);
@@ -144,8 +164,11 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
     const bool coal = OUT <= 1 && g.coal != 0;
     uint4* stg = reinterpret_cast<uint4*>(smW + g.w_bytes + (size_t)warp * 2048);
     uint32_t lt = 0;
-    for (int t = blockIdx.x; t < S; t += gridDim.x, ++lt) {
-      const int tyi = t / g.tiles_x, txi = t - tyi * g.tiles_x;
+    // tile coordinates advance incrementally (an integer division per tile sat on the epilogue's critical path)
+    const int step_y = (int)gridDim.x / g.tiles_x, step_x = (int)gridDim.x - step_y * g.tiles_x;
+    int tyi = (int)blockIdx.x / g.tiles_x, txi = (int)blockIdx.x - tyi * g.tiles_x;
+    for (int t = blockIdx.x; t < S; t += gridDim.x, ++lt, tyi += step_y, txi += step_x) {
+      if (txi >= g.tiles_x) { txi -= g.tiles_x; ++tyi; }
       const int oy = tyi * TM_TH + quad * 4 + (lane >> 3), ox = txi * TM_TW + (lane & 7);
       const bool ok = has_cols && oy < a.H && ox < a.W;
       const int64_t pix = (int64_t)oy * a.W + ox;
@@ -175,16 +198,16 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
       if (has_cols) {
         const uint32_t taddr = tmem_base + buf * (uint32_t)g.BN + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0;
         uint32_t v0[16], v1[16];
-        tmem_ld16(taddr, v0);
+        if (second16) {                                               // warp-uniform
+          tm_ld16_nowait(taddr, v0);
+          tm_ld16_nowait(taddr + 16, v1);
+          tm_ld_wait2(v0, v1);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = v0[i];
-        if (second16) {
-          tmem_ld16(taddr + 16, v1);
-#pragma unroll
-          for (int i = 0; i < 16; ++i) v[16 + i] = v1[i];
+          for (int i = 0; i < 16; ++i) { v[i] = v0[i]; v[16 + i] = v1[i]; }
         } else {
+          tmem_ld16(taddr, v0);
 #pragma unroll
-          for (int i = 0; i < 16; ++i) v[16 + i] = 0u;
+          for (int i = 0; i < 16; ++i) { v[i] = v0[i]; v[16 + i] = 0u; }
         }
       }
       // the accumulator is in registers: hand the TMEM buffer back before the stores
@@ -197,18 +220,38 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
 #pragma unroll
         for (int h = 0; h < 8; ++h) part[h] = 0.f;
         if (has_cols) {
+          if (a.head_n > 6) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const float x = tm_act(__uint_as_float(v[i]) + bias[i], ACT);
-            const float4 w0 = *reinterpret_cast<const float4*>(hw_s + (c0 + i) * 8);
-            const float4 w1 = *reinterpret_cast<const float4*>(hw_s + (c0 + i) * 8 + 4);
-            part[0] = fmaf(x, w0.x, part[0]); part[1] = fmaf(x, w0.y, part[1]);
-            part[2] = fmaf(x, w0.z, part[2]); part[3] = fmaf(x, w0.w, part[3]);
-            part[4] = fmaf(x, w1.x, part[4]); part[5] = fmaf(x, w1.y, part[5]);
-            part[6] = fmaf(x, w1.z, part[6]); part[7] = fmaf(x, w1.w, part[7]);
+            for (int i = 0; i < 32; ++i) {
+              const float x = tm_act(__uint_as_float(v[i]) + bias[i], ACT);
+              const float4 w0 = *reinterpret_cast<const float4*>(hw_s + (c0 + i) * 8);
+              const float4 w1 = *reinterpret_cast<const float4*>(hw_s + (c0 + i) * 8 + 4);
+              tm_fma2(part[0], part[1], x, w0.x, w0.y);
+              tm_fma2(part[2], part[3], x, w0.z, w0.w);
+              tm_fma2(part[4], part[5], x, w1.x, w1.y);
+              tm_fma2(part[6], part[7], x, w1.z, w1.w);
+            }
+          } else if (a.head_n > 4) {                                  // 5..6 heads (denoise_2: 6)
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const float x = tm_act(__uint_as_float(v[i]) + bias[i], ACT);
+              const float4 w0 = *reinterpret_cast<const float4*>(hw_s + (c0 + i) * 8);
+              const float2 w1 = *reinterpret_cast<const float2*>(hw_s + (c0 + i) * 8 + 4);
+              tm_fma2(part[0], part[1], x, w0.x, w0.y);
+              tm_fma2(part[2], part[3], x, w0.z, w0.w);
+              tm_fma2(part[4], part[5], x, w1.x, w1.y);
+            }
+          } else {                                                    // <= 4 heads (denoise_1: 3): half the weights
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const float x = tm_act(__uint_as_float(v[i]) + bias[i], ACT);
+              const float4 w0 = *reinterpret_cast<const float4*>(hw_s + (c0 + i) * 8);
+              tm_fma2(part[0], part[1], x, w0.x, w0.y);
+              tm_fma2(part[2], part[3], x, w0.z, w0.w);
+            }
           }
         }
-        float* ps = part_s + (quad * 32 + lane) * 8;
+        float* ps = part_s + ((buf * 4 + quad) * 32 + lane) * 8;
         if (half == 1) {
           *reinterpret_cast<float4*>(ps) = make_float4(part[0], part[1], part[2], part[3]);
           *reinterpret_cast<float4*>(ps + 4) = make_float4(part[4], part[5], part[6], part[7]);
@@ -223,7 +266,8 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
             *reinterpret_cast<float4*>(o + 4) = make_float4(part[4] + p1.x + __ldg(a.head_b + 4), part[5] + p1.y + __ldg(a.head_b + 5),
                                                             part[6] + p1.z + __ldg(a.head_b + 6), part[7] + p1.w + __ldg(a.head_b + 7));
         }
-        asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");     // part_s may be overwritten by the next tile
+        // no second barrier: the next tile uses the other half of part_s, and the tile after it is written only after
+        // that tile's barrier, which the reading warp reaches after these loads
         continue;
       }
       if (OUT <= 1 && coal) {
@@ -597,7 +641,7 @@ extern "C" int zt_conv2d_bf16_tma(const ZtConvBf16* dp, void* stream) {
   static const int coalesce = getenv("ZT_TMA_COALESCE") ? atoi(getenv("ZT_TMA_COALESCE")) : 1;
   g.coal = (coalesce && !d.out_f32 && !d.head_n) ? 1 : 0;
   const size_t stg_bytes = g.coal ? TM_STG_BYTES : 0;
-  const size_t budget = 226 * 1024 - TM_BAR_BYTES - g.w_bytes - stg_bytes - (d.head_n ? 6 * 1024 : 0);   // static smem of OUT = 3
+  const size_t budget = 226 * 1024 - TM_BAR_BYTES - g.w_bytes - stg_bytes - (d.head_n ? 10 * 1024 : 0);  // static smem of OUT = 3
   g.NA = (int)std::min<size_t>(g.single ? 6 : 4, budget / g.a_stage);
   ZT_REQUIRE(g.NA >= 2, "conv_bf16_tma: tile does not fit shared memory");
   const size_t smem = TM_BAR_BYTES + (size_t)g.NA * g.a_stage + g.w_bytes + stg_bytes;
@@ -607,7 +651,7 @@ extern "C" int zt_conv2d_bf16_tma(const ZtConvBf16* dp, void* stream) {
   a.weight = (const uint8_t*)d.weight; a.bias = d.bias; a.out = d.out; a.out_cs = d.out_cs;
   a.res = (const __nv_bfloat16*)d.res; a.res_cs = d.res_cs;
   a.H = d.H; a.W = d.W; a.cout = d.cout; a.ph = d.kh / 2; a.pw = d.kw / 2;
-  a.head_w = d.head_w; a.head_b = d.head_b;
+  a.head_w = d.head_w; a.head_b = d.head_b; a.head_n = d.head_n;
   const int gx = std::min(kNumSMs, g.S);
   cudaStream_t st = (cudaStream_t)stream;
 #define ZT_TM_LAUNCH(OUT, ACT)                                                                              \
@@ -615,7 +659,7 @@ extern "C" int zt_conv2d_bf16_tma(const ZtConvBf16* dp, void* stream) {
     static bool attr_done = false;                                                                          \
     if (!attr_done) {                                                                                       \
       ZT_CUDA(cudaFuncSetAttribute(conv_tma_kernel<OUT, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
-                                   ((OUT) == 3 ? 220 : 227) * 1024));    /* OUT = 3 has 6 KB static */       \
+                                   ((OUT) == 3 ? 216 : 227) * 1024));    /* OUT = 3 has 10 KB static */       \
       attr_done = true;                                                                                     \
     }                                                                                                       \
     ZT_CUDA(launch_pdl(conv_tma_kernel<OUT, ACT>, dim3(gx), dim3(TM_THREADS), smem, st, tmap, a, g));       \
