@@ -108,12 +108,20 @@ __global__ void __launch_bounds__(256) bn_train_apply_kernel(const float* __rest
                                                              const float* __restrict__ gamma,
                                                              const float* __restrict__ beta, int HW, int C, float eps,
                                                              int64_t total4) {
+  // per-channel constants once per block (the fp64 mean / variance / 1/sqrt chain used to run per element)
+  extern __shared__ float4 bn_cst[];      // [c] = (mean, rstd, gamma, beta)
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const double mean = stats[c * 2] / HW;
+    double var = stats[c * 2 + 1] / HW - mean * mean;
+    var = var < 0 ? 0 : var;
+    bn_cst[c] = make_float4((float)mean, (float)(1.0 / sqrt(var + (double)eps)), __ldg(gamma + c), __ldg(beta + c));
+  }
+  __syncthreads();
   const int c4n = C >> 2;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
        i += (int64_t)gridDim.x * blockDim.x) {
     const int cg = (int)(i % c4n);
     const int64_t pix = i / c4n;
-    const double* st = stats + (int64_t)cg * 8;
     const float4 v = __ldg(reinterpret_cast<const float4*>(x + pix * x_cs + cg * 4));
     float r[4] = {v.x, v.y, v.z, v.w};
     float4 rv = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -121,11 +129,8 @@ __global__ void __launch_bounds__(256) bn_train_apply_kernel(const float* __rest
     const float rr[4] = {rv.x, rv.y, rv.z, rv.w};
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
-      const double mean = st[e * 2] / HW;
-      double var = st[e * 2 + 1] / HW - mean * mean;
-      var = var < 0 ? 0 : var;
-      const float rstd = (float)(1.0 / sqrt(var + (double)eps));
-      float y = (r[e] - (float)mean) * rstd * __ldg(gamma + cg * 4 + e) + __ldg(beta + cg * 4 + e);
+      const float4 k = bn_cst[cg * 4 + e];
+      float y = (r[e] - k.x) * k.y * k.z + k.w;
       y = fmaxf(y, 0.f);
       r[e] = res ? rr[e] + y : y;
     }
@@ -239,8 +244,8 @@ extern "C" int zt_bn_train_nhwc_f32(const float* x, int x_cs, float* out, int ou
   if (int e = check_launch("instnorm_stats_kernel")) return e;
   const int64_t total4 = (int64_t)HW * (C >> 2);
   const int blocks = (int)std::min<int64_t>(ceil_div64(total4, 256), 8 * kNumSMs);
-  bn_train_apply_kernel<<<blocks, 256, 0, st>>>(x, x_cs, out, out_cs, res, res_cs, stats, gamma, beta, HW, C, eps,
-                                                total4);
+  bn_train_apply_kernel<<<blocks, 256, (size_t)C * sizeof(float4), st>>>(x, x_cs, out, out_cs, res, res_cs, stats, gamma,
+                                                                         beta, HW, C, eps, total4);
   if (int e = check_launch("bn_train_apply_kernel")) return e;
   if (running_mean && running_var) {
     bn_update_running_kernel<<<ceil_div(C, 128), 128, 0, st>>>(stats, running_mean, running_var, HW, C, momentum);

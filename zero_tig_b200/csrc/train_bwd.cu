@@ -429,6 +429,115 @@ __global__ void bn_bwd_apply_kernel(const float* __restrict__ x, int x_cs, const
     dx[p * dx_cs + c] = ga * rstd * (dy - m0 - xh * m1);
   }
 }
+// Vectorised forms of the two passes for C % 4 == 0 (every BatchNorm of the model: C = 64).  The scalar kernels above
+// evaluate the fp64 mean / variance / 1/sqrt chain per ELEMENT (the apply pass spent its time in fp64 division and
+// square roots: 550 us for a 960x540x64 tensor that moves 670 MB); here the per-channel constants are computed once
+// per thread (reduce) or once per block into shared memory (apply) - the same fp64 expressions, so the same fp32
+// constants and the same per-element fp32 arithmetic - and the tensor is streamed as float4.
+__global__ void __launch_bounds__(256) bn_bwd_reduce4_kernel(const float* __restrict__ x, int x_cs,
+                                                             const float* __restrict__ dout, int d_cs,
+                                                             const double* __restrict__ stats,
+                                                             const float* __restrict__ gamma,
+                                                             const float* __restrict__ beta, int HW, int C, float eps,
+                                                             int ppb, double* __restrict__ red) {
+  const int c4n = C >> 2, lanes = 256 / c4n;
+  const int cg = threadIdx.x % c4n, pl = threadIdx.x / c4n;
+  float mu[4], rstd[4], ga[4], be[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const int c = cg * 4 + e;
+    const double mean = stats[c * 2] / HW;
+    double var = stats[c * 2 + 1] / HW - mean * mean;
+    var = var < 0 ? 0 : var;
+    rstd[e] = (float)(1.0 / sqrt(var + (double)eps));
+    mu[e] = (float)mean;
+    ga[e] = gamma[c];
+    be[e] = beta[c];
+  }
+  const int p0 = blockIdx.x * ppb, p1 = pl < lanes ? min(HW, p0 + ppb) : 0;
+  double s0[4] = {0, 0, 0, 0}, s1[4] = {0, 0, 0, 0};
+  int p = p0 + pl;
+  for (; p + lanes < p1; p += 2 * lanes) {                       // two pixels in flight per thread
+    const float4 xa = __ldg(reinterpret_cast<const float4*>(x + (int64_t)p * x_cs + cg * 4));
+    const float4 da = __ldg(reinterpret_cast<const float4*>(dout + (int64_t)p * d_cs + cg * 4));
+    const float4 xb = __ldg(reinterpret_cast<const float4*>(x + (int64_t)(p + lanes) * x_cs + cg * 4));
+    const float4 db = __ldg(reinterpret_cast<const float4*>(dout + (int64_t)(p + lanes) * d_cs + cg * 4));
+    const float xv[2][4] = {{xa.x, xa.y, xa.z, xa.w}, {xb.x, xb.y, xb.z, xb.w}};
+    const float dv[2][4] = {{da.x, da.y, da.z, da.w}, {db.x, db.y, db.z, db.w}};
+#pragma unroll
+    for (int u = 0; u < 2; ++u)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float xh = (xv[u][e] - mu[e]) * rstd[e];
+        const float y = xh * ga[e] + be[e];
+        const float dy = y > 0.f ? dv[u][e] : 0.f;
+        s0[e] += (double)dy;
+        s1[e] += (double)(dy * xh);
+      }
+  }
+  for (; p < p1; p += lanes) {
+    const float4 xa = __ldg(reinterpret_cast<const float4*>(x + (int64_t)p * x_cs + cg * 4));
+    const float4 da = __ldg(reinterpret_cast<const float4*>(dout + (int64_t)p * d_cs + cg * 4));
+    const float xv[4] = {xa.x, xa.y, xa.z, xa.w}, dv[4] = {da.x, da.y, da.z, da.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float xh = (xv[e] - mu[e]) * rstd[e];
+      const float y = xh * ga[e] + be[e];
+      const float dy = y > 0.f ? dv[e] : 0.f;
+      s0[e] += (double)dy;
+      s1[e] += (double)(dy * xh);
+    }
+  }
+  __shared__ double rs[256 * 8];                                 // [thread][s0 x4 | s1 x4]
+#pragma unroll
+  for (int e = 0; e < 4; ++e) { rs[threadIdx.x * 8 + e] = s0[e]; rs[threadIdx.x * 8 + 4 + e] = s1[e]; }
+  __syncthreads();
+  for (int j = threadIdx.x; j < c4n * 8; j += 256) {
+    double acc = 0;
+    for (int l = 0; l < lanes; ++l) acc += rs[l * c4n * 8 + j];
+    const int g4 = j >> 3, e = j & 7;
+    atomicAdd(red + (g4 * 4 + (e & 3)) * 2 + (e >> 2), acc);
+  }
+}
+__global__ void __launch_bounds__(256) bn_bwd_apply4_kernel(const float* __restrict__ x, int x_cs,
+                                                            const float* __restrict__ dout, int d_cs,
+                                                            const double* __restrict__ stats,
+                                                            const double* __restrict__ red,
+                                                            const float* __restrict__ gamma,
+                                                            const float* __restrict__ beta, int HW, int C, float eps,
+                                                            float* __restrict__ dx, int dx_cs, int64_t total4) {
+  __shared__ float cst[256][6];                                  // mu, rstd, gamma, beta, mean(dy), mean(dy * xhat)
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const double mean = stats[c * 2] / HW;
+    double var = stats[c * 2 + 1] / HW - mean * mean;
+    var = var < 0 ? 0 : var;
+    cst[c][0] = (float)mean;
+    cst[c][1] = (float)(1.0 / sqrt(var + (double)eps));
+    cst[c][2] = gamma[c];
+    cst[c][3] = beta[c];
+    cst[c][4] = (float)(red[c * 2] / HW);
+    cst[c][5] = (float)(red[c * 2 + 1] / HW);
+  }
+  __syncthreads();
+  const int c4n = C >> 2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % c4n);
+    const int64_t p = i / c4n;
+    const float4 xa = __ldg(reinterpret_cast<const float4*>(x + p * x_cs + cg * 4));
+    const float4 da = __ldg(reinterpret_cast<const float4*>(dout + p * d_cs + cg * 4));
+    const float xv[4] = {xa.x, xa.y, xa.z, xa.w}, dv[4] = {da.x, da.y, da.z, da.w};
+    float r[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float* k = cst[cg * 4 + e];
+      const float xh = (xv[e] - k[0]) * k[1];
+      const float y = xh * k[2] + k[3];
+      const float dy = y > 0.f ? dv[e] : 0.f;
+      r[e] = k[2] * k[1] * (dy - k[4] - xh * k[5]);
+    }
+    *reinterpret_cast<float4*>(dx + p * dx_cs + cg * 4) = make_float4(r[0], r[1], r[2], r[3]);
+  }
+}
 // dgamma[c] += sum dy xhat; dbeta[c] += sum dy
 __global__ void bn_bwd_param_kernel(const double* __restrict__ red, int C, float* __restrict__ dgamma,
                                     float* __restrict__ dbeta) {
@@ -692,13 +801,24 @@ extern "C" int zt_bn_train_bwd_nhwc_f32(const float* x, int x_cs, const float* d
   const int threads = (256 / C) * C;
   const int blocks = std::max(1, std::min(ceil_div(HW, 64), 4 * kNumSMs));
   const int ppb = ceil_div(HW, blocks);
-  bn_bwd_reduce_kernel<<<ceil_div(HW, ppb), threads, 0, ZT_ST>>>(x, x_cs, dout, d_cs, stats, gamma, beta, HW, C, eps,
-                                                                  ppb, red);
-  if (int e = check_launch("bn_bwd_reduce_kernel")) return e;
   const int64_t total = (int64_t)HW * C;
-  bn_bwd_apply_kernel<<<grid_bw(total), 256, 0, ZT_ST>>>(x, x_cs, dout, d_cs, stats, red, gamma, beta, HW, C, eps, dx,
-                                                         dx_cs, total);
-  if (int e = check_launch("bn_bwd_apply_kernel")) return e;
+  const bool vec4 = (C & 3) == 0 && ((x_cs | d_cs | dx_cs) & 3) == 0 &&
+                    (((uintptr_t)x | (uintptr_t)dout | (uintptr_t)dx) & 15) == 0;
+  if (vec4) {
+    bn_bwd_reduce4_kernel<<<ceil_div(HW, ppb), 256, 0, ZT_ST>>>(x, x_cs, dout, d_cs, stats, gamma, beta, HW, C, eps, ppb,
+                                                                red);
+    if (int e = check_launch("bn_bwd_reduce4_kernel")) return e;
+    bn_bwd_apply4_kernel<<<grid_bw(total / 4), 256, 0, ZT_ST>>>(x, x_cs, dout, d_cs, stats, red, gamma, beta, HW, C, eps,
+                                                                dx, dx_cs, total / 4);
+    if (int e = check_launch("bn_bwd_apply4_kernel")) return e;
+  } else {
+    bn_bwd_reduce_kernel<<<ceil_div(HW, ppb), threads, 0, ZT_ST>>>(x, x_cs, dout, d_cs, stats, gamma, beta, HW, C, eps,
+                                                                    ppb, red);
+    if (int e = check_launch("bn_bwd_reduce_kernel")) return e;
+    bn_bwd_apply_kernel<<<grid_bw(total), 256, 0, ZT_ST>>>(x, x_cs, dout, d_cs, stats, red, gamma, beta, HW, C, eps, dx,
+                                                           dx_cs, total);
+    if (int e = check_launch("bn_bwd_apply_kernel")) return e;
+  }
   bn_bwd_param_kernel<<<ceil_div(C, 128), 128, 0, ZT_ST>>>(red, C, dgamma, dbeta);
   return check_launch("bn_bwd_param_kernel");
 }
