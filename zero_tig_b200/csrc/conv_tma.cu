@@ -32,6 +32,8 @@ constexpr int TM_BAR_BYTES = 1024;
 constexpr int TM_STG_BYTES = 8 * 2048;   // epilogue staging: 32 pixels x 64 B per epilogue warp
 
 struct TmGeom {
+  int thin;                               // single-copy mode with 32-byte pixel rows (cin <= 16): SWIZZLE_32B box of 16 channels,
+                                          // so neither TMA nor the tensor core touches the 96 zero bytes of a 128-byte row
   int single, PW;                         // single = 1: ONE copy of the tile with its halo (PW = 8 + kw - 1 pixels wide), taps are
                                           // unaligned shifted views of it (as conv_tc.cu); 0: kw pixel-shifted, atom-aligned copies
   int BN, kh, kw, nks, rows;              // rows = TM_TH + kh - 1
@@ -359,8 +361,12 @@ __global__ void __launch_bounds__(TM_THREADS, 1) conv_tma_kernel(const __grid_co
     const uint64_t desc0 = make_desc(0, 1024u);
     const uint32_t dhi = (uint32_t)(desc0 >> 32), dlo = (uint32_t)desc0;
     // single-copy mode: 8-pixel row groups of the patch are PW * 128 B apart, a tap is a row offset of (ky * PW + kx)
-    const uint32_t dhiA = g.single ? (uint32_t)(make_desc(0, (uint32_t)g.PW * 128u) >> 32) : dhi;
-    const uint32_t tap_y16 = g.single ? (uint32_t)g.PW * 8u : 64u, tap_x16 = g.single ? 8u : (g.copy_bytes >> 4);
+    // thin mode: the same views over 32-byte pixel rows (descriptor layout type SWIZZLE_32B, 8-pixel groups PW * 32 B apart)
+    const uint64_t desc_thin = ((make_desc(0, (uint32_t)g.PW * 32u) & ~(7ull << 61)) | (6ull << 61));
+    const uint32_t dhiA = g.thin ? (uint32_t)(desc_thin >> 32)
+                                 : g.single ? (uint32_t)(make_desc(0, (uint32_t)g.PW * 128u) >> 32) : dhi;
+    const uint32_t tap_y16 = g.thin ? (uint32_t)g.PW * 2u : g.single ? (uint32_t)g.PW * 8u : 64u;
+    const uint32_t tap_x16 = g.thin ? 2u : g.single ? 8u : (g.copy_bytes >> 4);
     const uint32_t smA16 = smem_u32(smA) >> 4, smW16 = smem_u32(smW) >> 4;
     const uint32_t a_stage16 = g.a_stage >> 4, wtap16 = g.w_tap >> 4;
     const uint32_t kh = g.kh, kw = g.kw, nks = g.nks;
@@ -538,20 +544,21 @@ static EncodeTiledFn encode_fn() {
 static std::mutex g_tm_mu;
 static std::map<std::tuple<const void*, int, int, int, int, int>, CUtensorMap> g_tm_cache;
 
-static int get_tensor_map(const void* base, int C, int W, int H, int rows, int box_w, CUtensorMap* out) {
+static int get_tensor_map(const void* base, int C, int W, int H, int rows, int box_w, int thin, CUtensorMap* out) {
   std::lock_guard<std::mutex> lk(g_tm_mu);
-  auto key = std::make_tuple(base, C, W, H, rows, box_w);
+  auto key = std::make_tuple(base, C, W, H, rows, box_w + (thin ? 1000 : 0));
   auto it = g_tm_cache.find(key);
   if (it != g_tm_cache.end()) { *out = it->second; return ZT_OK; }
   EncodeTiledFn fn = encode_fn();
   if (!fn) { set_error("conv_bf16_tma: cuTensorMapEncodeTiled is unavailable (no CUDA driver)"); return ZT_ERR_CUDA; }
   const cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H};
   const cuuint64_t strides[2] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2};
-  const cuuint32_t box[3] = {64u, (cuuint32_t)box_w, (cuuint32_t)rows};
+  const cuuint32_t box[3] = {thin ? 16u : 64u, (cuuint32_t)box_w, (cuuint32_t)rows};
   const cuuint32_t estr[3] = {1u, 1u, 1u};
   CUtensorMap m;
   const CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, thin ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { set_error("conv_bf16_tma: cuTensorMapEncodeTiled failed (%d)", (int)r); return ZT_ERR_CUDA; }
   if (g_tm_cache.size() > 256) g_tm_cache.clear();
@@ -626,8 +633,13 @@ extern "C" int zt_conv2d_bf16_tma(const ZtConvBf16* dp, void* stream) {
   static const int single_thr = getenv("ZT_TMA_SINGLE") ? atoi(getenv("ZT_TMA_SINGLE")) : 48 * 48;
   g.single = (d.kw == 3 && single_thr >= 0 && d.cin * g.BN <= single_thr) ? 1 : 0;
   g.PW = TM_TW + d.kw - 1;
+  // ZT_TMA_SW32=1: 32-byte pixel rows (SWIZZLE_32B box of 16 channels) for the 8 / 16-channel first layers.  Correct
+  // (tests pass) but measured SLOWER than the zero-padded 128-byte rows: 83 vs 73 us for 3 -> 48 at 1080p - the
+  // unaligned tap views cost more in the 32-byte layout and the layers are within 1.3-2x of the HBM floor anyway.
+  static const int sw32 = getenv("ZT_TMA_SW32") ? atoi(getenv("ZT_TMA_SW32")) : 0;
+  g.thin = (g.single && sw32 && d.cin <= 16) ? 1 : 0;
   if (g.single) {
-    g.copy_bytes = (uint32_t)(g.rows * g.PW) * 128u;                      // bytes the TMA box writes
+    g.copy_bytes = (uint32_t)(g.rows * g.PW) * (g.thin ? 32u : 128u);     // bytes the TMA box writes
     g.a_stage = (g.copy_bytes + 1023u) / 1024u * 1024u;
   } else {
     g.copy_bytes = (uint32_t)g.rows * 1024u;
@@ -646,7 +658,7 @@ extern "C" int zt_conv2d_bf16_tma(const ZtConvBf16* dp, void* stream) {
   ZT_REQUIRE(g.NA >= 2, "conv_bf16_tma: tile does not fit shared memory");
   const size_t smem = TM_BAR_BYTES + (size_t)g.NA * g.a_stage + g.w_bytes + stg_bytes;
   CUtensorMap tmap;
-  if (int e = get_tensor_map(d.in, d.cin, d.W, d.H, g.rows, g.single ? g.PW : TM_TW, &tmap)) return e;
+  if (int e = get_tensor_map(d.in, d.cin, d.W, d.H, g.rows, g.single ? g.PW : TM_TW, g.thin, &tmap)) return e;
   TmArgs a;
   a.weight = (const uint8_t*)d.weight; a.bias = d.bias; a.out = d.out; a.out_cs = d.out_cs;
   a.res = (const __nv_bfloat16*)d.res; a.res_cs = d.res_cs;
