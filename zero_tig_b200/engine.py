@@ -245,7 +245,8 @@ class RaftEngine:
         if "graph" not in ent:
             g = torch.cuda.CUDAGraph()
             n0 = _lib.launch_count()
-            with torch.cuda.graph(g):
+            # thread_local: host threads of the caller (decoders, writers) may make CUDA calls while this thread captures
+            with torch.cuda.graph(g, capture_error_mode="thread_local"):
                 out = self.forward_packed(x2, hp, wp, iters)
             ent.update(graph=g, out=out, last=self.last, n=_lib.launch_count() - n0)
         ent["graph"].replay()
@@ -675,7 +676,7 @@ class FrameEngine:
         if "graph" not in st:
             g = torch.cuda.CUDAGraph()
             n0 = _lib.launch_count()
-            with torch.cuda.graph(g):
+            with torch.cuda.graph(g, capture_error_mode="thread_local"):
                 out = self._steady_body(x, st, of_scale)
             st.update(graph=g, out=out, launches=_lib.launch_count() - n0)
         st["graph"].replay()
