@@ -138,10 +138,11 @@ class ClipRunner:
                  ahead=None, max_pending_writes=None):
         n = os.cpu_count() or 4
         self.process, self.save_root, self.dataset, self.size = process, save_root, dataset, size
-        self.decode_threads = decode_threads or max(2, n // 2)
-        self.encode_threads = encode_threads or max(2, n // 2)
+        # the PNG encoder is ~20x the cost of decode + resize (tools/clip_io_bench.py): it gets the cores
+        self.decode_threads = decode_threads or max(2, n // 4)
+        self.encode_threads = encode_threads or max(2, n)
         self.ahead = ahead or 2 * self.decode_threads
-        self.max_pending = max_pending_writes or 4 * self.encode_threads
+        self.max_pending = max_pending_writes or 3 * self.encode_threads
         self.frame_shape = None                       # (H, W): set by for_model -> pinned ring buffers
 
     @classmethod
@@ -160,11 +161,9 @@ class ClipRunner:
         lock = threading.Lock()
         errors = []
 
-        def write_pair(path, h2, h3):
+        def write_one(arr, path):
             try:
-                d, e = output_paths(path, self.save_root, self.dataset)
-                encode_png(h3, d)                     # predict.py: `output` (H3) is the *_denoise file
-                encode_png(h2, e)                     #             `enhance` (H2) the *_enhance file
+                encode_png(arr, path)
                 with lock:
                     written[0] += 1
             except Exception as ex:                   # surfaced by run()
@@ -184,9 +183,11 @@ class ClipRunner:
                     _frames.release_upto(i)
                     if errors:
                         raise errors[0]
-                    slots.acquire()                   # bounds host memory when the encoders fall behind
-                    epool.submit(write_pair, _seq[i], h2.numpy().copy(), h3.numpy().copy())
+                    d, e = output_paths(_seq[i], self.save_root, self.dataset)
+                    for arr, path in ((h3, d), (h2, e)):     # predict.py: `output` (H3) -> *_denoise, `enhance` (H2) -> *_enhance
+                        slots.acquire()               # bounds host memory when the encoders fall behind
+                        epool.submit(write_one, arr.numpy().copy(), path)
                 self.process(frames, emit, True)
         if errors:
             raise errors[0]
-        return written[0]
+        return written[0] // 2
