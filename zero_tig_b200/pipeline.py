@@ -12,6 +12,8 @@ multi_read_data.py:86-87,131) on the GPU; ``quantize_u8`` applies ``save_images`
 predict.py:57-61) on the GPU and returns the two 8-bit HWC images.  Together a 1080p frame moves 18.7 MB over PCIe
 instead of 74.6 MB.  No arithmetic of the model happens here: only copies, the two converters and stream events.
 """
+import os
+
 import torch
 
 from . import ops
@@ -111,9 +113,10 @@ def share_sms(models):
     inside it; each replica's kernel is limited to 148 // S CTAs (measured at 1080p: 3 shards x 49 CTAs 248 frames/s,
     3 x 148 222 frames/s; a lone sequence runs fastest on the full grid).  A single replica keeps the full grid."""
     n = len(models)
+    per = int(os.environ.get("ZT_SHARD_CTAS", "0")) or max(30, 148 // n)      # ZT_SHARD_CTAS: override for sweeps
     for m in models:
         eng = m.raft.engine()
-        eng.FUSED_MAX_CTAS = 0 if n <= 1 else max(30, 148 // n)
+        eng.FUSED_MAX_CTAS = 0 if n <= 1 else per
 
 
 class MultiShardPipeline:
