@@ -189,3 +189,45 @@ def test_runner_on_the_real_model_matches_direct_outputs(tmp_path, weights):
             assert got.shape == want.shape
             assert np.abs(got.astype(int) - want.astype(int)).max() <= 1, f       # graph replay vs eager: same kernels
             assert (got != want).mean() < 1e-3, f
+
+
+def test_sharded_prediction_covers_every_frame_once_with_halos(tmp_path):
+    """SURVEY 8e on the host side: three ranks over a 2-sequence tree (11 + 4 frames); every frame is written by
+    exactly one rank, a range that starts mid-sequence runs its halo frame first (as a new sequence) without writing it."""
+    from PIL import Image
+    from zero_tig_b200 import clip_io
+    paths = _tree(str(tmp_path / "in"), [("S01", "low_light_10", list(range(1, 12))), ("S02", "low_light_10", [1, 2, 3, 4])])
+    out = str(tmp_path / "out")
+    logs, total = [], 0
+    for rank in range(3):
+        todo, halos = clip_io.rank_paths(paths, rank, 3)
+        assert set(halos) <= set(todo) and len(todo) - len(halos) == 5
+        log = []
+        n = clip_io.predict_sharded(paths, out, lambda root: clip_io.ClipRunner(_fake_engine(log), root, size=None,
+                                                                               decode_threads=2, encode_threads=2),
+                                    rank=rank, world=3)
+        assert n == 5
+        total += n
+        logs.append((halos, log))
+    assert total == len(paths)
+    # rank 0: frames 1-5 of S01 (no halo); rank 1: halo 5 + frames 6-10; rank 2: halo 10 + frame 11, then S02 as its own sequence
+    assert logs[0] == ([], [("seq", 5, True)])
+    assert logs[1] == ([paths[4]], [("seq", 6, True)])
+    assert logs[2] == ([paths[9]], [("seq", 2, True), ("seq", 4, True)])
+    for p in paths:
+        d, e = clip_io.output_paths(p, out)
+        assert np.array_equal(np.asarray(Image.open(d)), np.asarray(Image.open(p).convert("RGB"))), p
+    assert sum(len(f) for _, _, f in os.walk(out)) == 2 * len(paths)       # no halo outputs, nothing twice
+
+
+def test_sharded_prediction_reads_torchrun_environment(tmp_path, monkeypatch):
+    from zero_tig_b200 import clip_io
+    paths = _tree(str(tmp_path / "in"), [("S01", "low_light_10", list(range(1, 9)))])
+    monkeypatch.setenv("RANK", "1")
+    monkeypatch.setenv("WORLD_SIZE", "2")
+    log = []
+    n = clip_io.predict_sharded(paths, str(tmp_path / "out"),
+                                lambda root: clip_io.ClipRunner(_fake_engine(log), root, size=None, decode_threads=2,
+                                                                encode_threads=2))
+    assert n == 4 and log == [("seq", 5, True)]                               # halo (frame 4) + frames 5-8
+    assert sorted(os.listdir(str(tmp_path / "out" / "S01" / "low_light_10")))[0] == "00005_denoise.png"

@@ -153,9 +153,12 @@ class ClipRunner:
         r.frame_shape = (H, W)
         return r
 
-    def run(self, paths):
+    def run(self, paths, skip=()):
         """Process ``paths`` (the dataloader's order) and write ``*_denoise.png`` / ``*_enhance.png`` for every frame.
-        Returns the number of frames written.  The first exception of any worker is re-raised here."""
+        Frames whose path is in ``skip`` are computed (they advance the recurrent state) but not written: the halo
+        frame of a frame-range shard (``shard.plan``).  Returns the number of frames written.  The first exception of
+        any worker is re-raised here."""
+        skip = frozenset(skip)
         written = [0]
         slots = threading.Semaphore(self.max_pending)
         lock = threading.Lock()
@@ -183,6 +186,8 @@ class ClipRunner:
                     _frames.release_upto(i)
                     if errors:
                         raise errors[0]
+                    if _seq[i] in skip:
+                        return
                     d, e = output_paths(_seq[i], self.save_root, self.dataset)
                     for arr, path in ((h3, d), (h2, e)):     # predict.py: `output` (H3) -> *_denoise, `enhance` (H2) -> *_enhance
                         slots.acquire()               # bounds host memory when the encoders fall behind
@@ -191,3 +196,31 @@ class ClipRunner:
         if errors:
             raise errors[0]
         return written[0] // 2
+
+
+def rank_paths(paths, rank, world):
+    """This rank's share of a dataloader-ordered frame list under ``shard.plan``: whole sequences first,
+    contiguous frame ranges of a long sequence otherwise, each range that starts mid-sequence preceded by its halo
+    frame.  Returns (paths to process, in order; halo paths to pass as ``skip``)."""
+    from . import shard
+    seqs = split_sequences(list(paths))
+    todo, halos = [], []
+    for w in shard.plan([len(s) for s in seqs], world)[rank]:
+        if w.halo >= 0:
+            todo.append(seqs[w.seq][w.halo])
+            halos.append(seqs[w.seq][w.halo])
+        todo.extend(seqs[w.seq][w.start:w.stop])
+    return todo, halos
+
+
+def predict_sharded(paths, save_root, make_runner, rank=None, world=None):
+    """One rank of a frame-range-sharded prediction run (no collective: every rank reads its frames and writes its
+    PNGs).  ``make_runner(save_root)`` builds this rank's ``ClipRunner`` (``ClipRunner.for_model`` on the GPU
+    box); ``rank`` / ``world`` default to torchrun's RANK / WORLD_SIZE.  Note that two consecutive ranges of the same
+    sequence stay two sequences for the runner: a range's halo is the frame before its first kept frame, so the path
+    rule that cuts sequences sees consecutive indices inside a range and a fresh start at each range's first path."""
+    rank = int(os.environ.get("RANK", "0")) if rank is None else rank
+    world = int(os.environ.get("WORLD_SIZE", "1")) if world is None else world
+    todo, halos = rank_paths(paths, rank, world)
+    return make_runner(save_root).run(todo, skip=halos)
+
